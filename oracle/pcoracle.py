@@ -1,0 +1,190 @@
+"""ctypes loader for the parity checkers under oracle/ -- TEST INFRASTRUCTURE, NOT PRODUCT.
+
+Two interchangeable back ends with the same methods:
+
+* ``Oracle("port")`` -- oracle/libpcnn_oracle.so, the CPU restatement (port_nn.cpp,
+  port_icp.cpp); always buildable.
+* ``Oracle("ref")``  -- oracle/_ref/libpcnn_ref.so (+ libpcnn_ref_icp.so): the reference's own
+  headers compiled unmodified (ref_nn.cpp drives Homework2/hw2/include/*.hpp; ref_icp.cpp
+  drives the vendored nanoflann.hpp).  Built only where /root/reference is mounted; the built
+  files travel to the GPU box.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+KDTREE, OCTREE = 0, 1
+
+_f32p = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int32)
+_i64p = C.POINTER(C.c_int64)
+_f64p = C.POINTER(C.c_double)
+
+
+def _ptr(a, t):
+    return a.ctypes.data_as(t) if a is not None else None
+
+
+def build_oracle(ref=True):
+    """Compile the checkers (building the checker is not using it)."""
+    subprocess.check_call(["make", "-s", "-C", _HERE, "port"])
+    if ref:
+        subprocess.check_call(["make", "-s", "-C", _HERE, "_ref"])
+
+
+def have(which):
+    if which == "port":
+        return os.path.exists(os.path.join(_HERE, "libpcnn_oracle.so"))
+    return os.path.exists(os.path.join(_HERE, "_ref", "libpcnn_ref.so"))
+
+
+def _xyz(a):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    assert a.ndim == 2 and a.shape[1] in (3, 4), a.shape
+    return a
+
+
+class Oracle:
+    def __init__(self, which="port"):
+        self.which = which
+        if which == "port":
+            self.nn = C.CDLL(os.path.join(_HERE, "libpcnn_oracle.so"))
+            self.icp_lib = self.nn
+            self.pfx = "pcport_"
+        elif which == "ref":
+            self.nn = C.CDLL(os.path.join(_HERE, "_ref", "libpcnn_ref.so"))
+            self.icp_lib = C.CDLL(os.path.join(_HERE, "_ref", "libpcnn_ref_icp.so"))
+            self.pfx = "pcref_"
+        else:
+            raise ValueError(which)
+        f = self._fn("build")
+        f.restype = C.c_void_p
+        f.argtypes = [C.c_int, _f32p, C.c_int64, C.c_int, C.c_int, C.c_double]
+        f = self._fn("destroy")
+        f.restype = None
+        f.argtypes = [C.c_void_p]
+        f = self._fn("knn")
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, _f32p, C.c_int64, C.c_int, C.c_int, _i32p, _f64p, _i32p, C.c_int]
+        f = self._fn("radius")
+        f.restype = C.c_int64
+        f.argtypes = [C.c_void_p, _f32p, C.c_int64, C.c_int, C.c_double, _i64p, C.c_int]
+        f = self._fn("radius_fetch")
+        f.restype = None
+        f.argtypes = [C.c_void_p, _i32p, _f64p]
+        for name in ("knn_checksum",):
+            f = self._fn(name)
+            f.restype = C.c_int64
+            f.argtypes = [C.c_void_p, _f32p, C.c_int64, C.c_int, C.c_int, C.c_int]
+        f = self._fn("radius_checksum")
+        f.restype = C.c_int64
+        f.argtypes = [C.c_void_p, _f32p, C.c_int64, C.c_int, C.c_double, C.c_int]
+        f = self._fn("hardware_threads")
+        f.restype = C.c_int
+        f.argtypes = []
+        f = getattr(self.icp_lib, self.pfx + "icp")
+        f.restype = C.c_int
+        f.argtypes = [_f32p, C.c_int64, _f32p, C.c_int64, _f32p, _f32p, C.c_int, C.c_float,
+                      C.c_float, C.c_int, C.c_int, C.c_int, _f32p, _i64p, _f32p, _i32p]
+        f = getattr(self.icp_lib, self.pfx + "nn1")
+        f.restype = C.c_int
+        f.argtypes = [_f32p, C.c_int64, _f32p, C.c_int64, _i32p, _f32p, C.c_int]
+        if which == "port":
+            f = self.nn.pcport_brute_knn
+            f.restype = C.c_int
+            f.argtypes = [_f32p, C.c_int64, C.c_int, _f32p, C.c_int64, C.c_int, C.c_int, _i32p,
+                          _f64p, C.c_int]
+
+    def _fn(self, name):
+        return getattr(self.nn, self.pfx + name)
+
+    def hardware_threads(self):
+        return int(self._fn("hardware_threads")())
+
+    # ---- index
+    def build(self, kind, xyz, leaf_size=32, min_extent=1e-4):
+        xyz = _xyz(xyz)
+        h = self._fn("build")(kind, _ptr(xyz, _f32p), xyz.shape[0], xyz.shape[1], leaf_size,
+                              float(min_extent))
+        return _Tree(self, h, xyz)
+
+    # ---- ICP (restated loop); returns dict
+    def icp(self, src, tar, tar_normals=None, init_T=None, max_iter=30, max_corres_dist=1.0,
+            loss_epsilon=0.0, mode=0, accum=1, nthreads=1, want_corr=False):
+        src = np.ascontiguousarray(src, dtype=np.float32).reshape(-1, 3)
+        tar = np.ascontiguousarray(tar, dtype=np.float32).reshape(-1, 3)
+        nrm = None if tar_normals is None else np.ascontiguousarray(tar_normals, np.float32).reshape(-1, 3)
+        T0 = np.eye(4, dtype=np.float32) if init_T is None else np.ascontiguousarray(init_T, np.float32)
+        T = np.zeros(16, np.float32)
+        info = np.zeros(4, np.int64)
+        loss = np.zeros(1, np.float32)
+        corr = np.zeros(src.shape[0], np.int32) if want_corr else None
+        getattr(self.icp_lib, self.pfx + "icp")(
+            _ptr(src, _f32p), src.shape[0], _ptr(tar, _f32p), tar.shape[0], _ptr(nrm, _f32p),
+            _ptr(T0, _f32p), max_iter, max_corres_dist, loss_epsilon, mode, accum, nthreads,
+            _ptr(T, _f32p), _ptr(info, _i64p), _ptr(loss, _f32p), _ptr(corr, _i32p))
+        return {"T": T.reshape(4, 4), "iters": int(info[0]), "converged": int(info[1]),
+                "status": int(info[2]), "pairs": int(info[3]), "loss": float(loss[0]), "corr": corr}
+
+    def nn1(self, tar, q, nthreads=1):
+        tar = np.ascontiguousarray(tar, dtype=np.float32).reshape(-1, 3)
+        q = np.ascontiguousarray(q, dtype=np.float32).reshape(-1, 3)
+        idx = np.zeros(q.shape[0], np.int32)
+        d2 = np.zeros(q.shape[0], np.float32)
+        getattr(self.icp_lib, self.pfx + "nn1")(_ptr(tar, _f32p), tar.shape[0], _ptr(q, _f32p),
+                                                q.shape[0], _ptr(idx, _i32p), _ptr(d2, _f32p), nthreads)
+        return idx, d2
+
+    def brute_knn(self, xyz, q, k, nthreads=1):
+        """Canonical answer: k smallest under (d2 double, index); returns (idx, d2)."""
+        assert self.which == "port"
+        xyz, q = _xyz(xyz), _xyz(q)
+        idx = np.zeros((q.shape[0], k), np.int32)
+        d2 = np.zeros((q.shape[0], k), np.float64)
+        self.nn.pcport_brute_knn(_ptr(xyz, _f32p), xyz.shape[0], xyz.shape[1], _ptr(q, _f32p),
+                                 q.shape[0], q.shape[1], k, _ptr(idx, _i32p), _ptr(d2, _f64p), nthreads)
+        return idx, d2
+
+
+class _Tree:
+    def __init__(self, lib, h, xyz):
+        self.lib, self.h, self.xyz = lib, h, xyz
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib._fn("destroy")(self.h)
+            self.h = None
+
+    def knn(self, q, k, nthreads=1, want_cmp=False):
+        q = _xyz(q)
+        idx = np.zeros((q.shape[0], k), np.int32)
+        dist = np.zeros((q.shape[0], k), np.float64)
+        cmp_ = np.zeros(q.shape[0], np.int32) if want_cmp else None
+        self.lib._fn("knn")(self.h, _ptr(q, _f32p), q.shape[0], q.shape[1], k, _ptr(idx, _i32p),
+                            _ptr(dist, _f64p), _ptr(cmp_, _i32p), nthreads)
+        return (idx, dist, cmp_) if want_cmp else (idx, dist)
+
+    def radius(self, q, r, nthreads=1):
+        q = _xyz(q)
+        off = np.zeros(q.shape[0] + 1, np.int64)
+        total = self.lib._fn("radius")(self.h, _ptr(q, _f32p), q.shape[0], q.shape[1], float(r),
+                                       _ptr(off, _i64p), nthreads)
+        idx = np.zeros(total, np.int32)
+        dist = np.zeros(total, np.float64)
+        self.lib._fn("radius_fetch")(self.h, _ptr(idx, _i32p), _ptr(dist, _f64p))
+        return off, idx, dist
+
+    def knn_checksum(self, q, k, nthreads=1):
+        q = _xyz(q)
+        return int(self.lib._fn("knn_checksum")(self.h, _ptr(q, _f32p), q.shape[0], q.shape[1], k, nthreads))
+
+    def radius_checksum(self, q, r, nthreads=1):
+        q = _xyz(q)
+        return int(self.lib._fn("radius_checksum")(self.h, _ptr(q, _f32p), q.shape[0], q.shape[1],
+                                                   float(r), nthreads))

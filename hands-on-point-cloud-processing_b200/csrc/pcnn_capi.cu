@@ -1,0 +1,230 @@
+// pcnn_capi.cu -- C ABI entry points for kNN / radius search (declared in include/pcnn.h).
+// Device-pointer variants validate and enqueue; host-pointer variants stage through HBM in
+// chunks on three streams so that the PCIe copies of one chunk overlap the kernels of the
+// next (the reference has no device boundary: Homework2/hw2/include/benchmark.hpp:59-72).
+#include <algorithm>
+#include <vector>
+#include "pcnn_internal.cuh"
+
+using namespace pcnn;
+
+namespace {
+
+constexpr int64_t HOST_CHUNK = 1 << 18;  // queries per pipeline stage
+constexpr int HOST_STREAMS = 3;
+
+struct StreamSet {
+    cudaStream_t s[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+    bool ok = true;
+    StreamSet() {
+        for (int i = 0; i < HOST_STREAMS; i++)
+            if (cudaStreamCreateWithFlags(&s[i], cudaStreamNonBlocking) != cudaSuccess) ok = false;
+    }
+    ~StreamSet() {
+        for (int i = 0; i < HOST_STREAMS; i++)
+            if (s[i]) cudaStreamDestroy(s[i]);
+    }
+};
+
+int check_query_args(const char* fn, const pcnn_index* index, const float* q, int64_t nq, int stride) {
+    PCNN_CHECK_ARG(index != nullptr, "%s: index is NULL", fn);
+    PCNN_CHECK_ARG(nq >= 0 && nq < (int64_t)0x7fffffff, "%s: nq=%lld out of range", fn, (long long)nq);
+    PCNN_CHECK_ARG(stride >= 3, "%s: stride must be >= 3 floats (got %d)", fn, stride);
+    PCNN_CHECK_ARG(nq == 0 || q != nullptr, "%s: query pointer is NULL", fn);
+    return PCNN_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pcnn_knn(const pcnn_index* index, const float* q_dev, int64_t nq, int stride, int k,
+             int32_t* out_idx_dev, float* out_dist_dev, double* out_dist64_dev, pcnn_stream stream) {
+    int rc = check_query_args("pcnn_knn", index, q_dev, nq, stride);
+    if (rc != PCNN_OK) return rc;
+    PCNN_CHECK_ARG(k >= 1, "pcnn_knn: k must be >= 1 (got %d)", k);
+    if (k > PCNN_MAX_K) { set_error("pcnn_knn: k=%d exceeds PCNN_MAX_K=%d", k, PCNN_MAX_K); return PCNN_ERR_UNSUPPORTED; }
+    PCNN_CHECK_ARG(nq == 0 || out_idx_dev != nullptr, "pcnn_knn: out_idx is NULL");
+    PCNN_CHECK_ARG((int64_t)nq * k < (int64_t)1 << 40, "pcnn_knn: nq*k too large");
+    DeviceGuard g(index->device);
+    if (!g.ok) { set_error("pcnn_knn: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
+    return launch_knn(index, q_dev, nq, stride, k, out_idx_dev, out_dist_dev, out_dist64_dev, (cudaStream_t)stream);
+}
+
+int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int stride, int k,
+                  int32_t* out_idx_host, float* out_dist_host, double* out_dist64_host) {
+    int rc = check_query_args("pcnn_knn_host", index, q_host, nq, stride);
+    if (rc != PCNN_OK) return rc;
+    PCNN_CHECK_ARG(k >= 1, "pcnn_knn_host: k must be >= 1 (got %d)", k);
+    if (k > PCNN_MAX_K) { set_error("pcnn_knn_host: k=%d exceeds PCNN_MAX_K=%d", k, PCNN_MAX_K); return PCNN_ERR_UNSUPPORTED; }
+    PCNN_CHECK_ARG(nq == 0 || out_idx_host != nullptr, "pcnn_knn_host: out_idx is NULL");
+    if (nq == 0) return PCNN_OK;
+    DeviceGuard g(index->device);
+    if (!g.ok) { set_error("pcnn_knn_host: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
+    StreamSet ss;
+    if (!ss.ok) { set_error("pcnn_knn_host: stream creation failed"); return PCNN_ERR_CUDA; }
+    const int64_t chunk = std::min<int64_t>(HOST_CHUNK, nq);
+    // per-stream staging buffers, reused round-robin (stream order protects the reuse)
+    float* dq[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+    int32_t* di[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+    float* dd[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+    double* dd64[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+    cudaError_t e = cudaSuccess;
+    const int nstreams = (int)std::min<int64_t>(HOST_STREAMS, (nq + chunk - 1) / chunk);
+    for (int i = 0; i < nstreams && e == cudaSuccess; i++) {
+        e = cudaMalloc(&dq[i], sizeof(float) * (size_t)chunk * stride);
+        if (e == cudaSuccess) e = cudaMalloc(&di[i], sizeof(int32_t) * (size_t)chunk * k);
+        if (e == cudaSuccess && out_dist_host) e = cudaMalloc(&dd[i], sizeof(float) * (size_t)chunk * k);
+        if (e == cudaSuccess && out_dist64_host) e = cudaMalloc(&dd64[i], sizeof(double) * (size_t)chunk * k);
+    }
+    if (e != cudaSuccess) {
+        set_error("pcnn_knn_host: staging allocation failed: %s", cudaGetErrorString(e));
+        rc = PCNN_ERR_NOMEM;
+    }
+    int c = 0;
+    for (int64_t q0 = 0; q0 < nq && rc == PCNN_OK; q0 += chunk, c++) {
+        const int b = c % nstreams;
+        const int64_t m = std::min<int64_t>(chunk, nq - q0);
+        cudaStream_t s = ss.s[b];
+        e = cudaMemcpyAsync(dq[b], q_host + q0 * stride, sizeof(float) * (size_t)m * stride, cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) { set_error("pcnn_knn_host: H2D failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; break; }
+        rc = launch_knn(index, dq[b], m, stride, k, di[b], dd[b], dd64[b], s);
+        if (rc != PCNN_OK) break;
+        e = cudaMemcpyAsync(out_idx_host + q0 * k, di[b], sizeof(int32_t) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess && out_dist_host)
+            e = cudaMemcpyAsync(out_dist_host + q0 * k, dd[b], sizeof(float) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess && out_dist64_host)
+            e = cudaMemcpyAsync(out_dist64_host + q0 * k, dd64[b], sizeof(double) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
+        if (e != cudaSuccess) { set_error("pcnn_knn_host: D2H failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; }
+    }
+    for (int i = 0; i < HOST_STREAMS; i++) {
+        e = cudaStreamSynchronize(ss.s[i]);
+        if (e != cudaSuccess && rc == PCNN_OK) {
+            set_error("pcnn_knn_host: device work failed: %s", cudaGetErrorString(e));
+            rc = PCNN_ERR_CUDA;
+        }
+    }
+    for (int i = 0; i < HOST_STREAMS; i++) { cudaFree(dq[i]); cudaFree(di[i]); cudaFree(dd[i]); cudaFree(dd64[i]); }
+    return rc;
+}
+
+int pcnn_radius_count(const pcnn_index* index, const float* q_dev, int64_t nq, int stride, double radius,
+                      int64_t* out_offsets_dev, int64_t* out_total_host, pcnn_stream stream) {
+    int rc = check_query_args("pcnn_radius_count", index, q_dev, nq, stride);
+    if (rc != PCNN_OK) return rc;
+    PCNN_CHECK_ARG(out_offsets_dev != nullptr, "pcnn_radius_count: out_offsets is NULL");
+    PCNN_CHECK_ARG(radius == radius, "pcnn_radius_count: radius is NaN");
+    DeviceGuard g(index->device);
+    if (!g.ok) { set_error("pcnn_radius_count: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
+    cudaStream_t s = (cudaStream_t)stream;
+    rc = launch_radius_count(index, q_dev, nq, stride, radius, out_offsets_dev, s);
+    if (rc != PCNN_OK) return rc;
+    if (out_total_host) {
+        PCNN_CUDA(cudaMemcpyAsync(out_total_host, out_offsets_dev + nq, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+        PCNN_CUDA(cudaStreamSynchronize(s));
+    }
+    return PCNN_OK;
+}
+
+int pcnn_radius_fill(const pcnn_index* index, const float* q_dev, int64_t nq, int stride, double radius,
+                     const int64_t* offsets_dev, int32_t* out_idx_dev, float* out_dist_dev,
+                     double* out_dist64_dev, pcnn_stream stream) {
+    int rc = check_query_args("pcnn_radius_fill", index, q_dev, nq, stride);
+    if (rc != PCNN_OK) return rc;
+    PCNN_CHECK_ARG(offsets_dev != nullptr, "pcnn_radius_fill: offsets is NULL");
+    PCNN_CHECK_ARG(out_idx_dev != nullptr || nq == 0, "pcnn_radius_fill: out_idx is NULL");
+    PCNN_CHECK_ARG(radius == radius, "pcnn_radius_fill: radius is NaN");
+    DeviceGuard g(index->device);
+    if (!g.ok) { set_error("pcnn_radius_fill: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
+    return launch_radius_fill(index, q_dev, nq, stride, radius, offsets_dev, out_idx_dev, out_dist_dev,
+                              out_dist64_dev, (cudaStream_t)stream);
+}
+
+int pcnn_radius_host(const pcnn_index* index, const float* q_host, int64_t nq, int stride, double radius,
+                     int64_t* offsets_host, int32_t* out_idx_host, float* out_dist_host,
+                     double* out_dist64_host, int64_t capacity) {
+    int rc = check_query_args("pcnn_radius_host", index, q_host, nq, stride);
+    if (rc != PCNN_OK) return rc;
+    PCNN_CHECK_ARG(offsets_host != nullptr, "pcnn_radius_host: offsets is NULL");
+    PCNN_CHECK_ARG(radius == radius, "pcnn_radius_host: radius is NaN");
+    PCNN_CHECK_ARG(capacity >= 0, "pcnn_radius_host: negative capacity");
+    DeviceGuard g(index->device);
+    if (!g.ok) { set_error("pcnn_radius_host: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
+    if (nq == 0) { offsets_host[0] = 0; return PCNN_OK; }
+    cudaStream_t s = nullptr;
+    PCNN_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    float* dq = nullptr;
+    int64_t* doff = nullptr;
+    int32_t* di = nullptr;
+    float* dd = nullptr;
+    double* dd64 = nullptr;
+    cudaError_t e = cudaMalloc(&dq, sizeof(float) * (size_t)nq * stride);
+    if (e == cudaSuccess) e = cudaMalloc(&doff, sizeof(int64_t) * ((size_t)nq + 1));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dq, q_host, sizeof(float) * (size_t)nq * stride, cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) { set_error("pcnn_radius_host: staging failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_NOMEM; }
+    int64_t total = 0;
+    if (rc == PCNN_OK) rc = launch_radius_count(index, dq, nq, stride, radius, doff, s);
+    if (rc == PCNN_OK) {
+        e = cudaMemcpyAsync(offsets_host, doff, sizeof(int64_t) * ((size_t)nq + 1), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) { set_error("pcnn_radius_host: count pass failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; }
+        else total = offsets_host[nq];
+    }
+    if (rc == PCNN_OK && total > capacity) {
+        set_error("pcnn_radius_host: %lld hits exceed capacity %lld", (long long)total, (long long)capacity);
+        rc = PCNN_ERR_CAPACITY;
+    }
+    if (rc == PCNN_OK && total > 0) {
+        PCNN_CHECK_ARG(out_idx_host != nullptr, "pcnn_radius_host: out_idx is NULL");
+        e = cudaMalloc(&di, sizeof(int32_t) * (size_t)total);
+        if (e == cudaSuccess && out_dist_host) e = cudaMalloc(&dd, sizeof(float) * (size_t)total);
+        if (e == cudaSuccess && out_dist64_host) e = cudaMalloc(&dd64, sizeof(double) * (size_t)total);
+        if (e != cudaSuccess) { set_error("pcnn_radius_host: output allocation failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_NOMEM; }
+        if (rc == PCNN_OK) rc = launch_radius_fill(index, dq, nq, stride, radius, doff, di, dd, dd64, s);
+        if (rc == PCNN_OK) {
+            e = cudaMemcpyAsync(out_idx_host, di, sizeof(int32_t) * (size_t)total, cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess && out_dist_host)
+                e = cudaMemcpyAsync(out_dist_host, dd, sizeof(float) * (size_t)total, cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess && out_dist64_host)
+                e = cudaMemcpyAsync(out_dist64_host, dd64, sizeof(double) * (size_t)total, cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+            if (e != cudaSuccess) { set_error("pcnn_radius_host: fill pass failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; }
+        }
+    }
+    cudaStreamSynchronize(s);
+    cudaFree(dq); cudaFree(doff); cudaFree(di); cudaFree(dd); cudaFree(dd64);
+    cudaStreamDestroy(s);
+    return rc;
+}
+
+int pcnn_icp_host(const pcnn_index* target, const float* tar_normals_host, const float* src_host,
+                  int64_t n_src, int stride, const float* init_T_host, const pcnn_icp_params* params,
+                  pcnn_icp_result* out_host) {
+    PCNN_CHECK_ARG(target && params && out_host && init_T_host, "pcnn_icp_host: NULL argument");
+    PCNN_CHECK_ARG(n_src >= 0 && stride >= 3, "pcnn_icp_host: bad n_src/stride");
+    PCNN_CHECK_ARG(n_src == 0 || src_host, "pcnn_icp_host: src is NULL");
+    PCNN_CHECK_ARG(params->mode == 0 || tar_normals_host || target->n == 0, "pcnn_icp_host: point-to-plane needs target normals");
+    DeviceGuard g(target->device);
+    if (!g.ok) { set_error("pcnn_icp_host: cannot select CUDA device %d (no CPU fallback exists)", target->device); return PCNN_ERR_CUDA; }
+    cudaStream_t s = nullptr;
+    PCNN_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    float *dsrc = nullptr, *dn = nullptr;
+    int rc = PCNN_OK;
+    cudaError_t e = cudaSuccess;
+    if (n_src > 0) {
+        e = cudaMalloc(&dsrc, sizeof(float) * (size_t)n_src * stride);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dsrc, src_host, sizeof(float) * (size_t)n_src * stride, cudaMemcpyHostToDevice, s);
+    }
+    if (e == cudaSuccess && params->mode == 1 && target->n > 0) {
+        e = cudaMalloc(&dn, sizeof(float) * 3 * (size_t)target->n);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dn, tar_normals_host, sizeof(float) * 3 * (size_t)target->n, cudaMemcpyHostToDevice, s);
+    }
+    if (e != cudaSuccess) { set_error("pcnn_icp_host: staging failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_NOMEM; }
+    if (rc == PCNN_OK) rc = pcnn_icp(target, dn, dsrc, n_src, stride, init_T_host, params, out_host, s);
+    cudaStreamSynchronize(s);
+    cudaFree(dsrc); cudaFree(dn);
+    cudaStreamDestroy(s);
+    return rc;
+}
+
+}  // extern "C"

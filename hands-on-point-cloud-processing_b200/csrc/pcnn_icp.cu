@@ -1,0 +1,610 @@
+// pcnn_icp.cu -- ICP iteration as one fused kernel (sm_100a) + on-device pose update.
+//
+// Replaces Registration::ICPpoint2point (Homework9/hw9/src/registration.cpp:862-1011) and
+// Registration::ICPpoint2plane (:710-859), whose iteration is: nanoflann 1-NN per source
+// point (:772-785, :925-941) -> gate on the squared distance -> gather pairs into dense
+// matrices (:788-815, :964-978) -> Kabsch SVD (:979-998) or normal equations (:818) ->
+// T_total = T_delta * T_total (:849, :1002) -> transformCloudInplace (:165-178, :851, :1003).
+//
+// Here one kernel per iteration does, per source point: apply the pending T_delta in float32
+// (same operation order as the reference, so the cloud stays bit-comparable), exact float32
+// 1-NN through the Morton hierarchy, the gate, and the per-pair terms; a warp-shuffle +
+// shared-memory reduction in double gives per-block partials, and the last block to finish
+// folds them in a fixed order (deterministic, no floating-point atomics) and solves the 3x3
+// SVD / 6x6 Cholesky on device.  The host never waits inside the loop.  The dense M x 6
+// matrix A of the reference is never materialised: only the 29 scalars of A^T A, A^T b, b^T b
+// and the count are carried.
+#include "pcnn_internal.cuh"
+#include "pcnn_search.cuh"
+
+struct pcnn_icp_state {
+    const pcnn_index* target = nullptr;
+    int device = 0;
+    int64_t n_src = 0;
+    pcnn_icp_params prm{};
+    float4* cur = nullptr;       // source cloud, current pose, Morton order, .w = global source index
+    float4* nrm = nullptr;       // target normals in the index's Morton order (mode 1)
+    double* partials = nullptr;  // [nblocks][32]
+    struct Dev* dev = nullptr;   // device-resident loop state
+    int nblocks = 0;
+};
+
+namespace pcnn {
+
+constexpr int ICP_THREADS = 128;
+constexpr int ICP_NS = PCNN_ICP_NSUMS;  // 32
+// sums layout: p2p  [0..2]=sum p  [3..5]=sum q  [6..14]=sum q_r*p_c  [28]=count
+//              p2pl [0..20]=upper triangle of A^T A  [21..26]=A^T b  [27]=b^T b  [28]=count
+//              [31] (as int64) = (global index of the last kept pair << 32) | float bits of its d2
+}  // namespace pcnn
+
+struct Dev {
+    float T[16];
+    float Rd[9];
+    float td[3];
+    double sums[pcnn::ICP_NS];
+    int iters;
+    int converged;
+    int status;
+    int done;
+    int unchanged;
+    float last_loss;
+    float loss;
+    long long last_pairs;
+    unsigned block_counter;
+};
+
+namespace pcnn {
+
+__device__ __forceinline__ void xform(const float* R, const float* t, float& x, float& y, float& z) {
+    // ((r0*x + r1*y) + r2*z) + t, float32, no FMA: transformCloudInplace, registration.cpp:165-178
+    const float nx = fadd(fadd(fadd(fmul(R[0], x), fmul(R[1], y)), fmul(R[2], z)), t[0]);
+    const float ny = fadd(fadd(fadd(fmul(R[3], x), fmul(R[4], y)), fmul(R[5], z)), t[1]);
+    const float nz = fadd(fadd(fadd(fmul(R[6], x), fmul(R[7], y)), fmul(R[8], z)), t[2]);
+    x = nx; y = ny; z = nz;
+}
+
+// One-sided Jacobi SVD, 3x3, double: A = U diag(s) V^T, s descending.
+__device__ void svd3_dev(const double* A, double* U, double* s, double* V) {
+    double W[9];
+    for (int i = 0; i < 9; i++) { W[i] = A[i]; V[i] = (i % 4 == 0) ? 1.0 : 0.0; }
+    for (int sweep = 0; sweep < 60; sweep++) {
+        double off = 0;
+        for (int p = 0; p < 2; p++)
+            for (int q = p + 1; q < 3; q++) {
+                double a = 0, b = 0, c = 0;
+                for (int r = 0; r < 3; r++) {
+                    a += W[r * 3 + p] * W[r * 3 + p];
+                    b += W[r * 3 + q] * W[r * 3 + q];
+                    c += W[r * 3 + p] * W[r * 3 + q];
+                }
+                off = fmax(off, fabs(c) / sqrt(fmax(a * b, 1e-300)));
+                if (fabs(c) <= 1e-300) continue;
+                const double zeta = (b - a) / (2.0 * c);
+                const double tt = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+                for (int r = 0; r < 3; r++) {
+                    const double wp = W[r * 3 + p], wq = W[r * 3 + q];
+                    W[r * 3 + p] = cs * wp - sn * wq;
+                    W[r * 3 + q] = sn * wp + cs * wq;
+                    const double vp = V[r * 3 + p], vq = V[r * 3 + q];
+                    V[r * 3 + p] = cs * vp - sn * vq;
+                    V[r * 3 + q] = sn * vp + cs * vq;
+                }
+            }
+        if (off < 1e-15) break;
+    }
+    double nrm[3];
+    int ord[3] = {0, 1, 2};
+    for (int c = 0; c < 3; c++) nrm[c] = sqrt(W[c] * W[c] + W[3 + c] * W[3 + c] + W[6 + c] * W[6 + c]);
+    for (int a = 0; a < 2; a++)
+        for (int b = a + 1; b < 3; b++)
+            if (nrm[ord[b]] > nrm[ord[a]]) { int t = ord[a]; ord[a] = ord[b]; ord[b] = t; }
+    double Vs[9];
+    for (int c = 0; c < 3; c++) {
+        const int o = ord[c];
+        s[c] = nrm[o];
+        for (int r = 0; r < 3; r++) {
+            U[r * 3 + c] = nrm[o] > 0 ? W[r * 3 + o] / nrm[o] : 0.0;
+            Vs[r * 3 + c] = V[r * 3 + o];
+        }
+    }
+    for (int i = 0; i < 9; i++) V[i] = Vs[i];
+    if (!(s[2] > 1e-300)) {  // rank-deficient: complete U with a cross product
+        U[2] = U[3] * U[7] - U[6] * U[4];
+        U[5] = U[6] * U[1] - U[0] * U[7];
+        U[8] = U[0] * U[4] - U[3] * U[1];
+    }
+}
+
+__device__ bool chol6_dev(const double* N, const double* g, double* x) {
+    double L[36];
+    for (int i = 0; i < 36; i++) L[i] = 0;
+    for (int i = 0; i < 6; i++)
+        for (int j = 0; j <= i; j++) {
+            double s = N[i * 6 + j];
+            for (int k = 0; k < j; k++) s -= L[i * 6 + k] * L[j * 6 + k];
+            if (i == j) {
+                if (!(s > 0)) return false;
+                L[i * 6 + i] = sqrt(s);
+            } else
+                L[i * 6 + j] = s / L[j * 6 + j];
+        }
+    double y[6];
+    for (int i = 0; i < 6; i++) {
+        double s = g[i];
+        for (int k = 0; k < i; k++) s -= L[i * 6 + k] * y[k];
+        y[i] = s / L[i * 6 + i];
+    }
+    for (int i = 5; i >= 0; i--) {
+        double s = y[i];
+        for (int k = i + 1; k < 6; k++) s -= L[k * 6 + i] * x[k];
+        x[i] = s / L[i * 6 + i];
+    }
+    return true;
+}
+
+// Pose update from the (all-reduced) sums: registration.cpp:948-1003 / :820-851.
+// Runs in one thread; every rank computes the identical result from identical sums.
+__device__ void icp_update_dev(Dev* st, int mode, float loss_epsilon) {
+    if (st->done) return;
+    const double* S = st->sums;
+    const double M = S[28];
+    float R[9], t[3];
+    float loss = 0.f;
+    bool ok = M > 0.5;
+    if (mode == 0) {
+        const long long packed = __double_as_longlong(S[31]);
+        if (ok) { const float d2 = __int_as_float((int)(packed & 0xffffffffLL)); loss = fmul(d2, d2); }  // :939
+    }
+    double x[6] = {0, 0, 0, 0, 0, 0};
+    if (mode == 1) {
+        double N[36], g[6];
+        int u = 0;
+        for (int r = 0; r < 6; r++)
+            for (int c = r; c < 6; c++) { N[r * 6 + c] = S[u]; N[c * 6 + r] = S[u]; u++; }
+        for (int r = 0; r < 6; r++) g[r] = S[21 + r];
+        ok = ok && chol6_dev(N, g, x);
+        if (ok) {
+            double xNx = 0, xg = 0;
+            for (int r = 0; r < 6; r++) {
+                for (int c = 0; c < 6; c++) xNx += x[r] * N[r * 6 + c] * x[c];
+                xg += x[r] * g[r];
+            }
+            loss = (float)(xNx - 2.0 * xg + S[27]);  // ||A x - b||^2, :820
+        }
+    }
+    st->last_pairs = (long long)(M + 0.5);
+    st->loss = loss;
+    if (fabsf(st->last_loss - loss) < loss_epsilon) st->unchanged++;
+    if (st->unchanged > 15) { st->converged = 1; st->done = 1; st->last_loss = loss; return; }
+    st->last_loss = loss;
+    if (!ok) { st->status = 1; st->done = 1; return; }
+    if (mode == 0) {
+        double pc[3], qc[3], H[9];
+        for (int a = 0; a < 3; a++) { pc[a] = S[a] / M; qc[a] = S[3 + a] / M; }
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) H[r * 3 + c] = S[6 + r * 3 + c] - M * qc[r] * pc[c];  // tar_c * src_c^T
+        double U[9], s[3], V[9], Rd[9];
+        svd3_dev(H, U, s, V);
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++)
+                Rd[r * 3 + c] = U[r * 3] * V[c * 3] + U[r * 3 + 1] * V[c * 3 + 1] + U[r * 3 + 2] * V[c * 3 + 2];
+        const double det = Rd[0] * (Rd[4] * Rd[8] - Rd[5] * Rd[7]) - Rd[1] * (Rd[3] * Rd[8] - Rd[5] * Rd[6]) +
+                           Rd[2] * (Rd[3] * Rd[7] - Rd[4] * Rd[6]);
+        if (det < 0) {  // :990-996 as written: V * diag(1,1,det) * U^T
+            const double B[3] = {1, 1, det};
+            for (int r = 0; r < 3; r++)
+                for (int c = 0; c < 3; c++)
+                    Rd[r * 3 + c] = V[r * 3] * B[0] * U[c * 3] + V[r * 3 + 1] * B[1] * U[c * 3 + 1] +
+                                    V[r * 3 + 2] * B[2] * U[c * 3 + 2];
+        }
+        for (int a = 0; a < 9; a++) R[a] = (float)Rd[a];
+        for (int r = 0; r < 3; r++)
+            t[r] = (float)(qc[r] - (Rd[r * 3] * pc[0] + Rd[r * 3 + 1] * pc[1] + Rd[r * 3 + 2] * pc[2]));
+    } else {
+        const float xf[6] = {(float)x[0], (float)x[1], (float)x[2], (float)x[3], (float)x[4], (float)x[5]};
+        R[0] = 1; R[1] = -xf[2]; R[2] = xf[1];
+        R[3] = xf[2]; R[4] = 1; R[5] = -xf[0];
+        R[6] = -xf[1]; R[7] = xf[0]; R[8] = 1;  // linearised, :843
+        t[0] = xf[3]; t[1] = xf[4]; t[2] = xf[5];
+    }
+    // T_total = T_delta * T_total in float32 (:849, :1002)
+    const float D[16] = {R[0], R[1], R[2], t[0], R[3], R[4], R[5], t[1], R[6], R[7], R[8], t[2], 0, 0, 0, 1};
+    float O[16];
+    for (int r = 0; r < 4; r++)
+        for (int c = 0; c < 4; c++)
+            O[r * 4 + c] = fadd(fadd(fadd(fmul(D[r * 4], st->T[c]), fmul(D[r * 4 + 1], st->T[4 + c])),
+                                     fmul(D[r * 4 + 2], st->T[8 + c])), fmul(D[r * 4 + 3], st->T[12 + c]));
+    for (int i = 0; i < 16; i++) st->T[i] = O[i];
+    for (int i = 0; i < 9; i++) st->Rd[i] = R[i];
+    for (int i = 0; i < 3; i++) st->td[i] = t[i];
+    st->iters++;
+}
+
+__global__ void icp_update_kernel(Dev* st, int mode, float loss_epsilon) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) icp_update_dev(st, mode, loss_epsilon);
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ long long warp_max_ll(long long v) {
+    for (int o = 16; o > 0; o >>= 1) {
+        long long u = __shfl_xor_sync(0xffffffffu, v, o);
+        v = u > v ? u : v;
+    }
+    return v;
+}
+
+// MODE 0 = point-to-point (16 sums), 1 = point-to-plane (29 sums).
+template <int MODE, bool FUSED>
+__global__ void __launch_bounds__(ICP_THREADS)
+icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __restrict__ nrm, int n_src,
+                      float max_corres_dist, float loss_epsilon, int leaf_log, Dev* __restrict__ st,
+                      double* __restrict__ partials) {
+    constexpr int NT = MODE == 0 ? 16 : 29;
+    __shared__ double s_part[ICP_THREADS / 32][ICP_NS];
+    __shared__ long long s_last[ICP_THREADS / 32];
+    __shared__ bool s_is_last;
+    if (st->done) return;  // uniform: loop already ended (converged / failed)
+    const int t = blockIdx.x * ICP_THREADS + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double v[NT];
+#pragma unroll
+    for (int i = 0; i < NT; i++) v[i] = 0.0;
+    long long last = -1;
+    if (t < n_src) {
+        float4 p = cur[t];
+        xform(st->Rd, st->td, p.x, p.y, p.z);  // pending T_delta of the previous iteration
+        cur[t] = p;
+        Best1f best;
+        nn1_thread(iv, p.x, p.y, p.z, leaf_log, best);
+        if (best.pos >= 0 && best.key < max_corres_dist) {  // gate on the SQUARED distance (:783, :936)
+            const float4 qpt = __ldg(iv.pts + best.pos);
+            if (MODE == 0) {
+                v[0] = p.x; v[1] = p.y; v[2] = p.z;
+                v[3] = qpt.x; v[4] = qpt.y; v[5] = qpt.z;
+                v[6] = (double)qpt.x * p.x; v[7] = (double)qpt.x * p.y; v[8] = (double)qpt.x * p.z;
+                v[9] = (double)qpt.y * p.x; v[10] = (double)qpt.y * p.y; v[11] = (double)qpt.y * p.z;
+                v[12] = (double)qpt.z * p.x; v[13] = (double)qpt.z * p.y; v[14] = (double)qpt.z * p.z;
+                v[15] = 1.0;
+                last = ((long long)__float_as_int(p.w) << 32) | (long long)(unsigned)__float_as_int(best.key);
+            } else {
+                const float4 nn = __ldg(nrm + best.pos);
+                // row of A and b in float32 exactly as written at registration.cpp:808-814
+                float a[6];
+                a[0] = fadd(fmul(nn.z, p.y), -fmul(nn.y, p.z));
+                a[1] = fadd(fmul(nn.x, p.z), -fmul(nn.z, p.x));
+                a[2] = fadd(fmul(nn.y, p.x), -fmul(nn.x, p.y));
+                a[3] = nn.x; a[4] = nn.y; a[5] = nn.z;
+                float b = fadd(fadd(fmul(nn.x, qpt.x), fmul(nn.y, qpt.y)), fmul(nn.z, qpt.z));
+                b = fadd(b, -fmul(nn.x, p.x));
+                b = fadd(b, -fmul(nn.y, p.y));
+                b = fadd(b, -fmul(nn.z, p.z));
+                int u = 0;
+#pragma unroll
+                for (int r = 0; r < 6; r++)
+#pragma unroll
+                    for (int c = r; c < 6; c++) v[u++] = (double)a[r] * (double)a[c];
+#pragma unroll
+                for (int r = 0; r < 6; r++) v[21 + r] = (double)a[r] * (double)b;
+                v[27] = (double)b * (double)b;
+                v[28] = 1.0;
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < NT; i++) {
+        const double s = warp_sum(v[i]);
+        if (lane == 0) s_part[warp][i] = s;
+    }
+    if (MODE == 0) {
+        const long long m = warp_max_ll(last);
+        if (lane == 0) s_last[warp] = m;
+    }
+    __syncthreads();
+    if (threadIdx.x < ICP_NS) {
+        const int slot = threadIdx.x;
+        int src = -1;  // which per-thread term feeds this slot (the count lives at [28] in both modes)
+        if (MODE == 0) src = slot < 15 ? slot : (slot == 28 ? 15 : -1);
+        else src = slot < 29 ? slot : -1;
+        double s = 0.0;
+        if (src >= 0) {
+#pragma unroll
+            for (int w2 = 0; w2 < ICP_THREADS / 32; w2++) s += s_part[w2][src];
+        }
+        if (MODE == 0 && slot == 31) {
+            long long m = s_last[0];
+            for (int w2 = 1; w2 < ICP_THREADS / 32; w2++) m = s_last[w2] > m ? s_last[w2] : m;
+            s = __longlong_as_double(m);
+        }
+        partials[(size_t)blockIdx.x * ICP_NS + slot] = s;
+    }
+    // last-block-done: fold the per-block partials in a fixed order
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned ticket = atomicAdd(&st->block_counter, 1u);
+        s_is_last = (ticket == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_is_last) return;
+    __threadfence();
+    {
+        const int col = threadIdx.x & 31, part = threadIdx.x >> 5;  // 4 row-strided partial sums per column
+        double s = 0.0;
+        long long m = -1;
+        for (int b = part; b < (int)gridDim.x; b += ICP_THREADS / 32) {
+            const double x = __ldcg(partials + (size_t)b * ICP_NS + col);
+            if (col == 31) { const long long xi = __double_as_longlong(x); m = xi > m ? xi : m; }
+            else s += x;
+        }
+        s_part[part][col] = (col == 31) ? __longlong_as_double(m) : s;
+    }
+    __syncthreads();
+    if (threadIdx.x < ICP_NS) {
+        const int col = threadIdx.x;
+        double r;
+        if (col == 31) {
+            long long m = __double_as_longlong(s_part[0][col]);
+            for (int p2 = 1; p2 < ICP_THREADS / 32; p2++) {
+                const long long xi = __double_as_longlong(s_part[p2][col]);
+                m = xi > m ? xi : m;
+            }
+            r = __longlong_as_double(m);
+        } else {
+            r = ((s_part[0][col] + s_part[1][col]) + s_part[2][col]) + s_part[3][col];
+        }
+        st->sums[col] = r;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        st->block_counter = 0;
+        if (FUSED) icp_update_dev(st, MODE, loss_epsilon);
+    }
+}
+
+}  // namespace pcnn
+
+// ------------------------------------------------------------------ host side
+namespace pcnn {
+
+__global__ void icp_init_kernel(const float* __restrict__ src, int n, int stride, long long index_base,
+                                const float* __restrict__ T0, float4* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* p = src + (size_t)i * stride;
+    float x = p[0], y = p[1], z = p[2];
+    const float R[9] = {T0[0], T0[1], T0[2], T0[4], T0[5], T0[6], T0[8], T0[9], T0[10]};
+    const float t[3] = {T0[3], T0[7], T0[11]};
+    xform(R, t, x, y, z);  // registration.cpp:872-875
+    out[i] = make_float4(x, y, z, __int_as_float((int)(index_base + i)));
+}
+
+__global__ void gather4_kernel(const float4* __restrict__ in, const unsigned* __restrict__ perm, int n,
+                               float4* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[perm[i]];
+}
+
+__global__ void permute_normals_kernel(const float4* __restrict__ pts, int n, const float* __restrict__ normals,
+                                       float4* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int o = __float_as_int(pts[i].w);
+    const float* v = normals + (size_t)o * 3;
+    out[i] = make_float4(v[0], v[1], v[2], 0.f);
+}
+
+__global__ void icp_state_init_kernel(Dev* st, const float* __restrict__ T0) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        for (int i = 0; i < 16; i++) st->T[i] = T0[i];
+        st->T[12] = 0; st->T[13] = 0; st->T[14] = 0; st->T[15] = 1;  // :910-913 keeps the last row
+        for (int i = 0; i < 9; i++) st->Rd[i] = (i % 4 == 0) ? 1.f : 0.f;
+        for (int i = 0; i < 3; i++) st->td[i] = 0.f;
+        for (int i = 0; i < ICP_NS; i++) st->sums[i] = 0.0;
+        st->iters = 0; st->converged = 0; st->status = 0; st->done = 0; st->unchanged = 0;
+        st->last_loss = 0.f; st->loss = 0.f; st->last_pairs = 0; st->block_counter = 0;
+    }
+}
+
+__global__ void __launch_bounds__(128)
+nn1_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride, const unsigned* __restrict__ perm,
+           int leaf_log, int32_t* __restrict__ out_idx, float* __restrict__ out_d2) {
+    const int t = blockIdx.x * 128 + threadIdx.x;
+    if (t >= nq) return;
+    const int qi = perm ? (int)perm[t] : t;
+    const float* qp = q + (size_t)qi * stride;
+    Best1f best;
+    nn1_thread(iv, qp[0], qp[1], qp[2], leaf_log, best);
+    out_idx[qi] = best.pos >= 0 ? best.idx : -1;
+    if (out_d2) out_d2[qi] = best.key;
+}
+
+int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq64, int stride, int32_t* out_idx,
+               float* out_d2, cudaStream_t s) {
+    const int nq = (int)nq64;
+    if (nq == 0) return PCNN_OK;
+    Scratch sc(s);
+    unsigned* perm = nullptr;
+    if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {
+        int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+        if (rc != PCNN_OK) return rc;
+    }
+    nn1_kernel<<<(nq + 127) / 128, 128, 0, s>>>(ix->view, q, nq, stride, perm, ix->opt_leaf_log, out_idx, out_d2);
+    PCNN_CUDA(cudaGetLastError());
+    return PCNN_OK;
+}
+
+static void icp_free(pcnn_icp_state* st) {
+    if (!st) return;
+    cudaFree(st->cur);
+    cudaFree(st->nrm);
+    cudaFree(st->partials);
+    cudaFree(st->dev);
+    delete st;
+}
+
+static int icp_launch_accumulate(pcnn_icp_state* st, bool fused, cudaStream_t s) {
+    if (st->n_src == 0) return PCNN_OK;
+    const pcnn_index* ix = st->target;
+    const int n = (int)st->n_src;
+    const int ll = ix->opt_leaf_log;
+#define PCNN_ICP_LAUNCH(MODE, FUSED)                                                             \
+    icp_accumulate_kernel<MODE, FUSED><<<st->nblocks, ICP_THREADS, 0, s>>>(                      \
+        ix->view, st->cur, st->nrm, n, st->prm.max_corres_dist, st->prm.loss_epsilon, ll, st->dev, st->partials)
+    if (st->prm.mode == 0) { if (fused) PCNN_ICP_LAUNCH(0, true); else PCNN_ICP_LAUNCH(0, false); }
+    else { if (fused) PCNN_ICP_LAUNCH(1, true); else PCNN_ICP_LAUNCH(1, false); }
+#undef PCNN_ICP_LAUNCH
+    PCNN_CUDA(cudaGetLastError());
+    return PCNN_OK;
+}
+
+}  // namespace pcnn
+
+using namespace pcnn;
+
+extern "C" {
+
+int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float* tar_normals_dev,
+                    const float* src_dev, int64_t n_src, int stride, const float* init_T_host,
+                    const pcnn_icp_params* params, int64_t src_index_base, pcnn_stream stream) {
+    PCNN_CHECK_ARG(out && target && params && init_T_host, "pcnn_icp_create: NULL argument");
+    *out = nullptr;
+    PCNN_CHECK_ARG(n_src >= 0 && n_src < 0x7fffffff, "pcnn_icp_create: n_src out of range");
+    PCNN_CHECK_ARG(stride >= 3, "pcnn_icp_create: stride must be >= 3");
+    PCNN_CHECK_ARG(params->mode == 0 || params->mode == 1, "pcnn_icp_create: mode must be 0 or 1");
+    PCNN_CHECK_ARG(params->max_iter >= 0, "pcnn_icp_create: max_iter must be >= 0");
+    PCNN_CHECK_ARG(params->mode == 0 || tar_normals_dev != nullptr || target->n == 0,
+                   "pcnn_icp_create: point-to-plane needs target normals");
+    PCNN_CHECK_ARG(n_src == 0 || src_dev != nullptr, "pcnn_icp_create: src is NULL");
+    PCNN_CHECK_ARG(src_index_base >= 0 && src_index_base + n_src < 0x7fffffff, "pcnn_icp_create: index base out of range");
+    DeviceGuard g(target->device);
+    if (!g.ok) { set_error("pcnn_icp_create: cannot select device %d", target->device); return PCNN_ERR_CUDA; }
+    cudaStream_t s = (cudaStream_t)stream;
+    pcnn_icp_state* st = new (std::nothrow) pcnn_icp_state;
+    if (!st) { set_error("pcnn_icp_create: host allocation failed"); return PCNN_ERR_NOMEM; }
+    st->target = target; st->device = target->device; st->n_src = n_src; st->prm = *params;
+    const int n = (int)n_src;
+    st->nblocks = (n + ICP_THREADS - 1) / ICP_THREADS;
+    if (st->nblocks < 1) st->nblocks = 1;
+    cudaError_t e = cudaMalloc(&st->cur, sizeof(float4) * (size_t)(n + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&st->partials, sizeof(double) * ICP_NS * (size_t)st->nblocks);
+    if (e == cudaSuccess) e = cudaMalloc(&st->dev, sizeof(Dev));
+    if (e == cudaSuccess && params->mode == 1) e = cudaMalloc(&st->nrm, sizeof(float4) * (size_t)(target->n + 1));
+    if (e != cudaSuccess) {
+        set_error("pcnn_icp_create: device allocation failed: %s", cudaGetErrorString(e));
+        icp_free(st);
+        return PCNN_ERR_NOMEM;
+    }
+    int rc = PCNN_OK;
+    {
+        Scratch sc(s);
+        float* T0 = nullptr;
+        float4* tmp = nullptr;
+        e = sc.get(&T0, 16);
+        if (e == cudaSuccess) e = sc.get(&tmp, (size_t)n + 1);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(T0, init_T_host, sizeof(float) * 16, cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) {
+            set_error("pcnn_icp_create: staging failed: %s", cudaGetErrorString(e));
+            rc = PCNN_ERR_CUDA;
+        } else {
+            icp_state_init_kernel<<<1, 32, 0, s>>>(st->dev, T0);
+            if (n > 0) {
+                icp_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(src_dev, n, stride, (long long)src_index_base, T0, tmp);
+                unsigned* perm = nullptr;
+                if (target->n > 0 && n > 1024) rc = sort_queries(target, (const float*)tmp, n, 4, &perm, sc, s);
+                if (rc == PCNN_OK) {
+                    if (perm) gather4_kernel<<<(n + 255) / 256, 256, 0, s>>>(tmp, perm, n, st->cur);
+                    else e = cudaMemcpyAsync(st->cur, tmp, sizeof(float4) * (size_t)n, cudaMemcpyDeviceToDevice, s);
+                }
+            }
+            if (rc == PCNN_OK && params->mode == 1 && target->n > 0)
+                permute_normals_kernel<<<((int)target->n + 255) / 256, 256, 0, s>>>(target->pts, (int)target->n,
+                                                                                     tar_normals_dev, st->nrm);
+            // init_T_host may be reused by the caller as soon as we return: wait for its copy
+            if (rc == PCNN_OK && (e != cudaSuccess || cudaGetLastError() != cudaSuccess)) {
+                set_error("pcnn_icp_create: launch failed");
+                rc = PCNN_ERR_CUDA;
+            }
+            cudaStreamSynchronize(s);
+        }
+    }
+    if (rc != PCNN_OK) { icp_free(st); return rc; }
+    *out = st;
+    return PCNN_OK;
+}
+
+int pcnn_icp_accumulate(pcnn_icp_state* st, pcnn_stream stream) {
+    PCNN_CHECK_ARG(st, "pcnn_icp_accumulate: NULL state");
+    DeviceGuard g(st->device);
+    return icp_launch_accumulate(st, false, (cudaStream_t)stream);
+}
+
+double* pcnn_icp_sums_dev(pcnn_icp_state* st) { return st ? st->dev->sums : nullptr; }
+
+int pcnn_icp_update(pcnn_icp_state* st, pcnn_stream stream) {
+    PCNN_CHECK_ARG(st, "pcnn_icp_update: NULL state");
+    DeviceGuard g(st->device);
+    icp_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(st->dev, st->prm.mode, st->prm.loss_epsilon);
+    PCNN_CUDA(cudaGetLastError());
+    return PCNN_OK;
+}
+
+int pcnn_icp_finish(pcnn_icp_state* st, pcnn_icp_result* out_host, pcnn_stream stream) {
+    PCNN_CHECK_ARG(st && out_host, "pcnn_icp_finish: NULL argument");
+    DeviceGuard g(st->device);
+    Dev h;
+    PCNN_CUDA(cudaMemcpyAsync(&h, st->dev, sizeof(Dev), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PCNN_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    std::memcpy(out_host->T, h.T, sizeof(h.T));
+    out_host->iters = h.iters;
+    out_host->converged = h.converged;
+    out_host->status = h.status;
+    out_host->last_loss = h.last_loss;
+    out_host->last_pairs = h.last_pairs;
+    return PCNN_OK;
+}
+
+int pcnn_icp_destroy(pcnn_icp_state* st) {
+    if (!st) return PCNN_OK;
+    DeviceGuard g(st->device);
+    cudaDeviceSynchronize();
+    icp_free(st);
+    return PCNN_OK;
+}
+
+int pcnn_icp(const pcnn_index* target, const float* tar_normals_dev, const float* src_dev, int64_t n_src,
+             int stride, const float* init_T_host, const pcnn_icp_params* params, pcnn_icp_result* out_host,
+             pcnn_stream stream) {
+    PCNN_CHECK_ARG(out_host, "pcnn_icp: out is NULL");
+    pcnn_icp_state* st = nullptr;
+    int rc = pcnn_icp_create(&st, target, tar_normals_dev, src_dev, n_src, stride, init_T_host, params, 0, stream);
+    if (rc != PCNN_OK) return rc;
+    DeviceGuard g(st->device);
+    if (n_src == 0 || target->n == 0) {
+        // no correspondences can exist: report status 1 without iterating
+        rc = pcnn_icp_finish(st, out_host, stream);
+        if (rc == PCNN_OK && params->max_iter > 0) out_host->status = 1;
+    } else {
+        for (int it = 0; it < params->max_iter && rc == PCNN_OK; it++)
+            rc = icp_launch_accumulate(st, true, (cudaStream_t)stream);  // fused update, no host sync
+        if (rc == PCNN_OK) rc = pcnn_icp_finish(st, out_host, stream);
+    }
+    cudaStreamSynchronize((cudaStream_t)stream);
+    icp_free(st);
+    return rc;
+}
+
+int pcnn_nn1_f32(const pcnn_index* index, const float* q_dev, int64_t nq, int stride, int32_t* out_idx_dev,
+                 float* out_d2_dev, pcnn_stream stream) {
+    PCNN_CHECK_ARG(index && out_idx_dev, "pcnn_nn1_f32: NULL argument");
+    PCNN_CHECK_ARG(nq >= 0 && nq < 0x7fffffff && stride >= 3, "pcnn_nn1_f32: bad nq/stride");
+    PCNN_CHECK_ARG(nq == 0 || q_dev, "pcnn_nn1_f32: q is NULL");
+    DeviceGuard g(index->device);
+    return launch_nn1(index, q_dev, nq, stride, out_idx_dev, out_d2_dev, (cudaStream_t)stream);
+}
+
+}  // extern "C"

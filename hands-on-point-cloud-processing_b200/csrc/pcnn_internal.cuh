@@ -1,0 +1,99 @@
+// pcnn_internal.cuh -- host-side handle layout and helpers shared by the translation units.
+#pragma once
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include "../../include/pcnn.h"
+#include "pcnn_common.cuh"
+
+struct pcnn_index {
+    int kind = 0;
+    int device = 0;
+    int64_t n = 0;
+    int leaf_size = 32;
+    double min_extent = 0;
+    float4* pts = nullptr;
+    unsigned long long* gcode = nullptr;
+    float4* box = nullptr;
+    float* cube = nullptr;  // device [8]: min.xyz, inv_cell, max.xyz, side
+    pcnn::IndexView view{};
+    size_t bytes = 0;
+    float build_ms = 0.f;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;  // bracket the last build
+    // query-side options (pcnn_set_option)
+    int opt_sort_queries = 1;
+    int opt_method = 0;
+    int opt_leaf_log = 1;       // thread-per-query leaf = 2^leaf_log groups
+    int opt_warp_leaf_log = 2;  // warp-per-query leaf = 32 points
+};
+
+namespace pcnn {
+
+void set_error(const char* fmt, ...);
+
+#define PCNN_CUDA(call)                                                                     \
+    do {                                                                                    \
+        cudaError_t e__ = (call);                                                           \
+        if (e__ != cudaSuccess) {                                                           \
+            pcnn::set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call,              \
+                            cudaGetErrorString(e__));                                       \
+            return e__ == cudaErrorMemoryAllocation ? PCNN_ERR_NOMEM : PCNN_ERR_CUDA;       \
+        }                                                                                   \
+    } while (0)
+
+#define PCNN_CHECK_ARG(cond, ...)              \
+    do {                                       \
+        if (!(cond)) {                         \
+            pcnn::set_error(__VA_ARGS__);      \
+            return PCNN_ERR_INVALID;           \
+        }                                      \
+    } while (0)
+
+// RAII device switch
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+// Stream-ordered scratch allocation that is returned on scope exit.
+struct Scratch {
+    cudaStream_t s;
+    void* p[16];
+    int np = 0;
+    explicit Scratch(cudaStream_t s_) : s(s_) {}
+    template <typename T>
+    cudaError_t get(T** out, size_t count) {
+        void* q = nullptr;
+        cudaError_t e = cudaMallocAsync(&q, count * sizeof(T) + 16, s);
+        if (e == cudaSuccess) p[np++] = q;
+        *out = (T*)q;
+        return e;
+    }
+    ~Scratch() {
+        for (int i = 0; i < np; i++) cudaFreeAsync(p[i], s);
+    }
+};
+
+// kernels / launchers implemented across the .cu files
+int launch_knn(const pcnn_index* ix, const float* q, int64_t nq, int stride, int k, int32_t* out_idx,
+               float* out_dist, double* out_dist64, cudaStream_t s);
+int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq, int stride, double radius,
+                        int64_t* out_offsets, cudaStream_t s);
+int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq, int stride, double radius,
+                       const int64_t* offsets, int32_t* out_idx, float* out_dist, double* out_dist64,
+                       cudaStream_t s);
+int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq, int stride, int32_t* out_idx,
+               float* out_d2, cudaStream_t s);
+// Morton order of a query batch: perm[i] = original id of the i-th query along the curve.
+int sort_queries(const pcnn_index* ix, const float* q, int64_t nq, int stride, unsigned** perm_out,
+                 Scratch& scratch, cudaStream_t s);
+
+}  // namespace pcnn

@@ -1,0 +1,143 @@
+// pcnn_sort.cuh -- hand-written LSD radix sort (8-bit digits) of (key, uint32 value) pairs,
+// used for the Morton-code sort of the index build and for ordering query batches.
+// Replaces the reference's per-node median selection (Homework2/hw2/include/kdtree.hpp:57-109,
+// :208-261) and 8-way recursive partition (octree.hpp:36-90) as the spatial ordering step.
+//
+// Per pass: rs_hist (per-tile digit histogram, digit-major [256][ntiles]) -> rs_scan
+// (exclusive scan of that table) -> rs_scatter (stable rank inside the tile via
+// __match_any_sync + per-warp digit counters, then scatter).  HBM traffic per pass:
+// read keys twice + values once, write both once.
+#pragma once
+#include "pcnn_common.cuh"
+
+namespace pcnn {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
+constexpr int RS_WARPS = RS_THREADS / 32;
+
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS)
+rs_hist(const KeyT* __restrict__ keys, int n, int shift, unsigned* __restrict__ hist, int ntiles) {
+    __shared__ unsigned h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * RS_TILE;
+#pragma unroll
+    for (int it = 0; it < RS_ITEMS; it++) {
+        int i = base + it * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(unsigned)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[(size_t)threadIdx.x * ntiles + blockIdx.x] = h[threadIdx.x];
+}
+
+// Exclusive scan of `total` counters in place, one block of 1024 threads.
+static __global__ void __launch_bounds__(1024) rs_scan(unsigned* __restrict__ a, int total) {
+    __shared__ unsigned part[1024];
+    const int t = threadIdx.x;
+    const int chunk = (total + 1023) / 1024;
+    const int lo = min(t * chunk, total), hi = min(lo + chunk, total);
+    unsigned s = 0;
+    for (int i = lo; i < hi; i++) s += a[i];
+    part[t] = s;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {  // Hillis-Steele inclusive scan
+        unsigned v = (t >= d) ? part[t - d] : 0u;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    unsigned run = part[t] - s;
+    for (int i = lo; i < hi; i++) {
+        unsigned v = a[i];
+        a[i] = run;
+        run += v;
+    }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS)
+rs_scatter(const KeyT* __restrict__ kin, const unsigned* __restrict__ vin, KeyT* __restrict__ kout,
+           unsigned* __restrict__ vout, int n, int shift, const unsigned* __restrict__ offs,
+           int ntiles) {
+    __shared__ unsigned wcount[RS_WARPS][256];
+    __shared__ unsigned dbase[256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&wcount[0][0])[i] = 0;
+    __syncthreads();
+
+    // warp-striped ownership keeps the in-tile order = (warp, item, lane) = global index order
+    const int wbase = blockIdx.x * RS_TILE + warp * (32 * RS_ITEMS);
+    KeyT key[RS_ITEMS];
+    unsigned local[RS_ITEMS];
+#pragma unroll
+    for (int it = 0; it < RS_ITEMS; it++) {
+        int i = wbase + it * 32 + lane;
+        key[it] = (i < n) ? kin[i] : (KeyT)~(KeyT)0;  // padding sorts last, never written
+    }
+#pragma unroll
+    for (int it = 0; it < RS_ITEMS; it++) {
+        unsigned d = (unsigned)(key[it] >> shift) & 255u;
+        unsigned peers = __match_any_sync(0xffffffffu, d);
+        int leader = __ffs(peers) - 1;
+        unsigned rank = __popc(peers & ((1u << lane) - 1u));
+        unsigned b = 0;
+        if (lane == leader) {
+            b = wcount[warp][d];
+            wcount[warp][d] = b + __popc(peers);
+        }
+        b = __shfl_sync(0xffffffffu, b, leader);
+        local[it] = b + rank;
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // digit = threadIdx.x: exclusive prefix over the warps + global base of (digit, tile)
+        unsigned run = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) {
+            unsigned c = wcount[w][threadIdx.x];
+            wcount[w][threadIdx.x] = run;
+            run += c;
+        }
+        dbase[threadIdx.x] = offs[(size_t)threadIdx.x * ntiles + blockIdx.x];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < RS_ITEMS; it++) {
+        int i = wbase + it * 32 + lane;
+        if (i < n) {
+            unsigned d = (unsigned)(key[it] >> shift) & 255u;
+            unsigned pos = dbase[d] + wcount[warp][d] + local[it];
+            kout[pos] = key[it];
+            vout[pos] = vin[i];
+        }
+    }
+}
+
+// Sort (keys, vals) of length n by the low `bits` bits of the key.  k0/v0 hold the input;
+// k1/v1 are scratch of the same size; hist is scratch of 256*ceil(n/RS_TILE) unsigned.
+// Returns 0 if the result is in (k0, v0), 1 if it is in (k1, v1).
+template <typename KeyT>
+inline int radix_sort_pairs(KeyT* k0, unsigned* v0, KeyT* k1, unsigned* v1, unsigned* hist, int n,
+                            int bits, cudaStream_t s) {
+    if (n <= 0) return 0;
+    const int ntiles = (n + RS_TILE - 1) / RS_TILE;
+    int cur = 0;
+    for (int shift = 0; shift < bits; shift += 8) {
+        KeyT* ki = cur ? k1 : k0;
+        KeyT* ko = cur ? k0 : k1;
+        unsigned* vi = cur ? v1 : v0;
+        unsigned* vo = cur ? v0 : v1;
+        rs_hist<KeyT><<<ntiles, RS_THREADS, 0, s>>>(ki, n, shift, hist, ntiles);
+        rs_scan<<<1, 1024, 0, s>>>(hist, 256 * ntiles);
+        rs_scatter<KeyT><<<ntiles, RS_THREADS, 0, s>>>(ki, vi, ko, vo, n, shift, hist, ntiles);
+        cur ^= 1;
+    }
+    return cur;
+}
+
+inline size_t radix_hist_elems(int n) { return (size_t)256 * ((n + RS_TILE - 1) / RS_TILE); }
+
+}  // namespace pcnn

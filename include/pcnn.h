@@ -1,0 +1,205 @@
+/* pcnn.h -- C ABI of the B200-native nearest-neighbour + ICP hot path.
+ *
+ * Drop-in boundary for the nearest-neighbour path of yf26/Hands-On-Point-Cloud-Processing.
+ * The reference has no FFI; its operator API for this path is a set of C++ free functions
+ * and result types (citations relative to the reference tree):
+ *
+ *   KDTreeConstruction / KDTreeDestruction      Homework2/hw2/include/kdtree.hpp:419-435
+ *   KDTreeKNNSearch / KDTreeRadiusNNSearch      kdtree.hpp:329-364 / :367-402
+ *   OctreeConstruction / OctreeDestruction      Homework2/hw2/include/octree.hpp:242-277
+ *   OctreeKNNSearch / OctreeRadiusNNSearch      octree.hpp:143-186 / :189-237
+ *   KNNResultSet / RadiusNNResultSet            Homework2/hw2/include/resultSet.hpp:28-93 / :96-142
+ *   the per-query batch loop                    Homework2/hw2/include/benchmark.hpp:30-43, :59-72
+ *   Registration::ICPpoint2point / 2plane       Homework9/hw9/src/registration.cpp:862-1011 / :710-859
+ *   nanoflann 1-NN as ICP uses it               registration.cpp:772-785, :925-941
+ *
+ * Every entry point below names the reference interface it replaces.  Plain pointers and
+ * sizes only; no C++ or torch types.  hands-on-point-cloud-processing_b200/compat/pcnn_compat.hpp
+ * restores the reference's own names on top of this header.
+ *
+ * Conventions
+ *  - All functions return an int status: PCNN_OK (0) or a negative PCNN_ERR_*; the message
+ *    of the last failure on the calling thread is available from pcnn_last_error().
+ *  - Pointers named *_dev are device pointers on the index's device; *_host are host
+ *    pointers (pageable or pinned).  `stream` is a cudaStream_t passed as void* (NULL =
+ *    the legacy default stream).  Device-pointer entry points only ENQUEUE work on `stream`
+ *    and return; host-pointer entry points copy in, run, copy out and return when the
+ *    results are in the caller's buffers.
+ *  - Points and queries are float32 with `stride` floats between consecutive points
+ *    (3 = packed xyz, 4 = KITTI xyzi / float4).  The reference widens float32 input to
+ *    double (test.hpp:24-29); this ABI takes the float32 originals, which is lossless.
+ *  - There is no CPU fallback: without a CUDA device every compute entry point fails with
+ *    PCNN_ERR_CUDA.
+ *
+ * Result contract
+ *  - distance key  d2 = ((dx*dx) + dy*dy) + dz*dz  in IEEE double, dx = p - q widened from
+ *    float32, no FMA -- the reference's own arithmetic (kdtree.hpp:341-346);
+ *    reported distance = sqrt(d2), correctly rounded, as the reference stores it.
+ *  - kNN rows: the k smallest under (d2, original index), ascending.  The reference breaks
+ *    exact-distance ties by tree visit order (resultSet.hpp:69-90); the two differ only
+ *    inside an exact tie group straddling the k-th place.  Rows with fewer than k points
+ *    available are padded with index -1 and distance +inf.
+ *  - radius rows: every point with sqrt(d2) <= radius (inclusive, resultSet.hpp:134), in
+ *    ascending original index (the reference's order is traversal order; compare as sets).
+ */
+#ifndef PCNN_H
+#define PCNN_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCNN_VERSION 100
+
+#define PCNN_OK 0
+#define PCNN_ERR_INVALID (-1)     /* bad argument */
+#define PCNN_ERR_CUDA (-2)        /* CUDA runtime error / no device */
+#define PCNN_ERR_NOMEM (-3)       /* device or host allocation failed */
+#define PCNN_ERR_UNSUPPORTED (-4) /* argument outside the supported range (e.g. k > PCNN_MAX_K) */
+#define PCNN_ERR_CAPACITY (-5)    /* caller's output buffer too small; required size reported */
+
+#define PCNN_KDTREE 0 /* handle created for the KDTree* entry points */
+#define PCNN_OCTREE 1 /* handle created for the Octree* entry points */
+
+#define PCNN_MAX_K 128
+
+typedef struct pcnn_index pcnn_index;         /* opaque spatial index, per-handle ownership */
+typedef struct pcnn_icp_state pcnn_icp_state; /* opaque ICP iteration state */
+typedef void* pcnn_stream;                    /* cudaStream_t */
+
+const char* pcnn_last_error(void);
+int pcnn_version(void);
+/* Number of visible CUDA devices (0 if none); never fails. */
+int pcnn_device_count(void);
+
+/* ------------------------------------------------------------------ index build
+ * Replaces KDTreeConstruction(db, leaf_size) (kdtree.hpp:419-429) and
+ * OctreeConstruction(db, leaf_size, min_extent) (octree.hpp:242-271).
+ * `kind` records which family of entry points the handle serves; both kinds return the
+ * same neighbour sets.  `leaf_size` and `min_extent` are accepted for signature parity;
+ * leaf_size >= 1 and min_extent >= 0 are validated, the device index chooses its own
+ * bucket size.  The input cloud is copied; the caller may free it after the call returns
+ * (device variant: after `stream` has passed the call).
+ * Built on device: bounding box -> 63-bit Morton codes -> LSD radix sort -> float4 cloud in
+ * Morton order -> implicit binary hierarchy of AABBs over 8-point groups. */
+int pcnn_index_build(pcnn_index** out, int kind, const float* xyz_dev, int64_t n, int stride,
+                     int leaf_size, double min_extent, int device, pcnn_stream stream);
+int pcnn_index_build_host(pcnn_index** out, int kind, const float* xyz_host, int64_t n,
+                          int stride, int leaf_size, double min_extent, int device);
+/* Replaces KDTreeDestruction() / OctreeDestruction() (kdtree.hpp:431-435, octree.hpp:273-277),
+ * but frees exactly this handle. */
+int pcnn_index_destroy(pcnn_index* index);
+
+typedef struct {
+    int64_t n_points;
+    int32_t kind;
+    int32_t device;
+    int32_t n_levels;     /* levels of the implicit AABB hierarchy */
+    int32_t group_size;   /* points per base group */
+    int64_t device_bytes; /* HBM held by the handle */
+    float bbox_min[3];
+    float bbox_max[3];
+    float build_ms;       /* device time of the last build (CUDA events) */
+} pcnn_index_info;
+int pcnn_index_get_info(const pcnn_index* index, pcnn_index_info* out);
+
+/* ------------------------------------------------------------------ kNN
+ * Replaces, for nq queries at once, the loop body of benchmark.hpp:61-66:
+ *     KNNResultSet rs(k);  K?TreeKNNSearch / OctreeKNNSearch(root, db, rs, query);
+ * out_idx [nq*k] int32 original point indices; out_dist [nq*k] float32 and/or
+ * out_dist64 [nq*k] double distances (either may be NULL); rows ascending by (d2, index).
+ * 1 <= k <= PCNN_MAX_K. */
+int pcnn_knn(const pcnn_index* index, const float* q_dev, int64_t nq, int stride, int k,
+             int32_t* out_idx_dev, float* out_dist_dev, double* out_dist64_dev,
+             pcnn_stream stream);
+int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int stride, int k,
+                  int32_t* out_idx_host, float* out_dist_host, double* out_dist64_host);
+
+/* Query-side knobs (all have working defaults).  `sort_queries`: 1 = order queries along
+ * the Morton curve before the search (default), 0 = caller's order, e.g. already coherent.
+ * `method`: 0 = auto, 1 = thread-per-query traversal, 2 = warp-per-query traversal,
+ * 3 = brute-force tiles.  Returns PCNN_ERR_INVALID for unknown values. */
+int pcnn_set_option(pcnn_index* index, const char* name, int value);
+
+/* ------------------------------------------------------------------ radius search
+ * Replaces, for nq queries at once, benchmark.hpp:68-71:
+ *     RadiusNNResultSet rs(radius);  K?TreeRadiusNNSearch / OctreeRadiusNNSearch(...);
+ * Two passes, CSR output.  pcnn_radius_count fills out_offsets_dev[nq+1] (exclusive scan of
+ * the per-query hit counts, so out_offsets[nq] = total hits); if out_total_host is not NULL
+ * the call waits for the stream and stores the total there.  pcnn_radius_fill writes the
+ * hits of query i at [offsets[i], offsets[i+1]) in ascending original index. */
+int pcnn_radius_count(const pcnn_index* index, const float* q_dev, int64_t nq, int stride,
+                      double radius, int64_t* out_offsets_dev, int64_t* out_total_host,
+                      pcnn_stream stream);
+int pcnn_radius_fill(const pcnn_index* index, const float* q_dev, int64_t nq, int stride,
+                     double radius, const int64_t* offsets_dev, int32_t* out_idx_dev,
+                     float* out_dist_dev, double* out_dist64_dev, pcnn_stream stream);
+/* Host variant: offsets_host[nq+1] always filled; hits are written only if `capacity`
+ * (in hits) suffices, else PCNN_ERR_CAPACITY is returned with offsets_host valid so the
+ * caller can size its buffers from offsets_host[nq] and call again. */
+int pcnn_radius_host(const pcnn_index* index, const float* q_host, int64_t nq, int stride,
+                     double radius, int64_t* offsets_host, int32_t* out_idx_host,
+                     float* out_dist_host, double* out_dist64_host, int64_t capacity);
+
+/* ------------------------------------------------------------------ ICP
+ * Replaces Registration::ICPpoint2point (registration.cpp:862-1011) and ICPpoint2plane
+ * (:710-859) minus the normal-space sampling done before the loop (:728-729, :880-881):
+ * the caller passes the clouds the loop should run on.  Parameter meaning follows
+ * Registration::setICPparams (registration.hpp:126-137): max_corres_dist gates the SQUARED
+ * 1-NN distance (registration.cpp:783, :936); the loop stops early once
+ * |last_loss - loss| < loss_epsilon has held more than 15 times (:828-838, :948-958). */
+typedef struct {
+    int32_t max_iter;
+    float max_corres_dist;
+    float loss_epsilon;
+    int32_t mode; /* 0 = point-to-point, 1 = point-to-plane */
+} pcnn_icp_params;
+
+typedef struct {
+    float T[16];       /* row-major 4x4 T_total: R = T[0..2][0..2], t = T[0..2][3] */
+    int32_t iters;     /* iterations whose update was applied */
+    int32_t converged; /* 1 if the unchanged-loss rule fired */
+    int32_t status;    /* 0 ok; 1 = an iteration had no correspondences or a singular system */
+    float last_loss;
+    int64_t last_pairs; /* correspondences kept in the last executed iteration */
+} pcnn_icp_result;
+
+/* Whole loop on one GPU: no host synchronisation per iteration; one at the end to return
+ * the result.  `target` indexes the target cloud; tar_normals_dev ([n_target*3] packed,
+ * original target order) is required for mode 1, ignored for mode 0; init_T is a host
+ * row-major 4x4 (the reference's init_R / init_t). */
+int pcnn_icp(const pcnn_index* target, const float* tar_normals_dev, const float* src_dev,
+             int64_t n_src, int stride, const float* init_T_host, const pcnn_icp_params* params,
+             pcnn_icp_result* out_host, pcnn_stream stream);
+int pcnn_icp_host(const pcnn_index* target, const float* tar_normals_host,
+                  const float* src_host, int64_t n_src, int stride, const float* init_T_host,
+                  const pcnn_icp_params* params, pcnn_icp_result* out_host);
+
+/* Split-phase form for source clouds sharded over several GPUs (one process per GPU): each
+ * rank holds the full target index and its slice of the source.  Per iteration:
+ *     pcnn_icp_accumulate(st, stream);      fused transform + 1-NN + gate + partial sums
+ *     <all-reduce(sum) PCNN_ICP_NSUMS doubles at pcnn_icp_sums_dev(st) on `stream`>
+ *     pcnn_icp_update(st, stream);          solve + pose update, replicated on every rank
+ * Nothing synchronises with the host until pcnn_icp_finish. */
+#define PCNN_ICP_NSUMS 32
+int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float* tar_normals_dev,
+                    const float* src_dev, int64_t n_src, int stride, const float* init_T_host,
+                    const pcnn_icp_params* params, int64_t src_index_base, pcnn_stream stream);
+int pcnn_icp_accumulate(pcnn_icp_state* st, pcnn_stream stream);
+double* pcnn_icp_sums_dev(pcnn_icp_state* st);
+int pcnn_icp_update(pcnn_icp_state* st, pcnn_stream stream);
+int pcnn_icp_finish(pcnn_icp_state* st, pcnn_icp_result* out_host, pcnn_stream stream);
+int pcnn_icp_destroy(pcnn_icp_state* st);
+
+/* Exact float32 1-NN of every query against the index, as the ICP loop uses it
+ * (nanoflann.hpp:383-408 key: ((dx*dx)+dy*dy)+dz*dz in float32, dx = q - p; lowest index
+ * wins an exact tie).  out_idx [nq], out_d2 [nq]. */
+int pcnn_nn1_f32(const pcnn_index* index, const float* q_dev, int64_t nq, int stride,
+                 int32_t* out_idx_dev, float* out_d2_dev, pcnn_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCNN_H */

@@ -1,0 +1,171 @@
+"""The reference's own Python names for this path, backed by the CUDA library.
+
+Mirrors Homework2/hw2/script/result_set.py:16-89, kdtree.py:183-250 and octree.py:109-194:
+same function names, same argument order and meaning.  ``root`` is an ``Index`` instead of a
+``Node`` / ``Octant``; ``db`` is accepted and ignored by the searches (the reference passes it
+to every call, kdtree.py:183) because the index owns a copy of the cloud.
+
+The single-query functions fill a result set exactly as the reference does (one launch per
+query: correct, slow).  The ``*_batch`` functions hoist the loop of benchmark.py:58-72 into
+one call and are the intended fast path.
+"""
+import numpy as np
+
+from .api import KDTREE, OCTREE
+from .index import Index
+
+
+class DistIndex:
+    """result_set.py:4-13"""
+
+    def __init__(self, distance, index):
+        self.distance = distance
+        self.index = index
+
+    def __lt__(self, other):
+        return self.distance < other.distance
+
+    def __str__(self):
+        return "Distance = %s, Index = %s" % (self.distance, self.index)
+
+
+class KNNResultSet:
+    """result_set.py:16-61: bounded ascending list, capacity k, slots start at (1e10, 0)."""
+
+    def __init__(self, capacity):
+        self.capacity = capacity
+        self.count = 0
+        self.worst_dist = 1e10
+        self.dist_index_list = [DistIndex(self.worst_dist, 0) for _ in range(capacity)]
+        self.comparision_count = 0
+
+    def size(self):
+        return self.count
+
+    def full(self):
+        return self.count == self.capacity
+
+    def get_worst_dist(self):
+        return self.worst_dist
+
+    def list(self):
+        for item in self.dist_index_list:
+            print(item)
+
+    def add_point(self, dist, index):
+        self.comparision_count += 1
+        if dist > self.worst_dist:
+            return
+        if self.count < self.capacity:
+            self.count += 1
+        i = self.count - 1
+        while i > 0:
+            if self.dist_index_list[i - 1].distance > dist:
+                self.dist_index_list[i] = DistIndex(self.dist_index_list[i - 1].distance,
+                                                    self.dist_index_list[i - 1].index)
+                i -= 1
+            else:
+                break
+        self.dist_index_list[i].distance = dist
+        self.dist_index_list[i].index = index
+        self.worst_dist = self.dist_index_list[self.capacity - 1].distance
+
+    def _fill(self, idx_row, dist_row):
+        for j in range(self.capacity):
+            if idx_row[j] >= 0:
+                self.dist_index_list[j] = DistIndex(float(dist_row[j]), int(idx_row[j]))
+                self.count = j + 1
+        self.worst_dist = self.dist_index_list[self.capacity - 1].distance
+
+
+class RadiusNNResultSet:
+    """result_set.py:64-89: unbounded list of hits with dist <= radius."""
+
+    def __init__(self, radius):
+        self.radius = radius
+        self.count = 0
+        self.worst_dist = radius
+        self.dist_index_list = []
+        self.comparision_count = 0
+
+    def get_worst_dist(self):
+        return self.radius
+
+    def size(self):
+        return self.count
+
+    def list(self):
+        for item in self.dist_index_list:
+            print(item)
+
+    def add_point(self, distance, index):
+        self.comparision_count += 1
+        if distance > self.radius:
+            return
+        self.count += 1
+        self.dist_index_list.append(DistIndex(distance, index))
+
+
+def kdtree_construction(db_np, leaf_size):
+    """kdtree.py:240-250"""
+    return Index(db_np, kind=KDTREE, leaf_size=leaf_size)
+
+
+def octree_construction(db_np, leaf_size, min_extent):
+    """octree.py:184-194"""
+    return Index(db_np, kind=OCTREE, leaf_size=leaf_size, min_extent=min_extent)
+
+
+def _knn_single(root, result_set, query):
+    q = np.asarray(query, dtype=np.float32).reshape(1, -1)[:, :3]
+    idx, dist = root.knn(q, result_set.capacity, dist="f64")
+    result_set._fill(idx[0], dist[0])
+    return False
+
+
+def _radius_single(root, result_set, query):
+    q = np.asarray(query, dtype=np.float32).reshape(1, -1)[:, :3]
+    _, idx, dist = root.radius(q, result_set.radius, dist="f64")
+    for d, i in zip(dist, idx):
+        result_set.add_point(float(d), int(i))
+    return False
+
+
+def kdtree_knn_search(root, db, result_set, query):
+    """kdtree.py:183-204"""
+    return _knn_single(root, result_set, query)
+
+
+def kdtree_radius_search(root, db, result_set, query):
+    """kdtree.py:207-228"""
+    return _radius_single(root, result_set, query)
+
+
+def octree_knn_search(root, db, result_set, query):
+    """octree.py:109-143"""
+    return _knn_single(root, result_set, query)
+
+
+def octree_radius_search(root, db, result_set, query):
+    """octree.py:146-181"""
+    return _radius_single(root, result_set, query)
+
+
+def knn_search_batch(root, queries, k, dist="f64"):
+    """The loop of benchmark.py:58-66 as one call: (idx[nq,k], dist[nq,k])."""
+    return root.knn(queries, k, dist=dist)
+
+
+def radius_search_batch(root, queries, radius, dist="f64"):
+    """The loop of benchmark.py:68-71 as one call: CSR (offsets, idx, dist)."""
+    return root.radius(queries, radius, dist=dist)
+
+
+def read_velodyne_bin(path, duplicate_last=False):
+    """KITTI .bin (x, y, z, intensity float32) -> (N, 3) float32; kdtree.py:253-264.
+    ``duplicate_last=True`` reproduces the C++ reader's extra copy of the last point
+    (Homework2/hw2/include/test.hpp:24-29)."""
+    pts = np.fromfile(path, dtype=np.float32).reshape(-1, 4)[:, :3]
+    if duplicate_last and len(pts):
+        pts = np.concatenate([pts, pts[-1:]], axis=0)
+    return np.ascontiguousarray(pts)

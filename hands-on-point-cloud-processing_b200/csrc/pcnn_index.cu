@@ -147,6 +147,8 @@ static void free_index(pcnn_index* ix) {
     cudaFree(ix->cube);
     if (ix->ev_begin) cudaEventDestroy(ix->ev_begin);
     if (ix->ev_end) cudaEventDestroy(ix->ev_end);
+    if (ix->prof0) cudaEventDestroy(ix->prof0);
+    if (ix->prof1) cudaEventDestroy(ix->prof1);
     delete ix;
 }
 
@@ -331,6 +333,15 @@ int pcnn_index_get_info(const pcnn_index* index, pcnn_index_info* out) {
     return PCNN_OK;
 }
 
+int pcnn_get_profile(const pcnn_index* index, float* main_kernel_ms) {
+    PCNN_CHECK_ARG(index && main_kernel_ms, "pcnn_get_profile: NULL argument");
+    PCNN_CHECK_ARG(index->opt_profile && index->prof0, "pcnn_get_profile: option \"profile\" is not set");
+    DeviceGuard g(index->device);
+    PCNN_CUDA(cudaEventSynchronize(index->prof1));
+    PCNN_CUDA(cudaEventElapsedTime(main_kernel_ms, index->prof0, index->prof1));
+    return PCNN_OK;
+}
+
 int pcnn_set_option(pcnn_index* index, const char* name, int value) {
     PCNN_CHECK_ARG(index && name, "pcnn_set_option: NULL argument");
     if (!std::strcmp(name, "sort_queries")) {
@@ -339,6 +350,14 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
     } else if (!std::strcmp(name, "method")) {
         PCNN_CHECK_ARG(value >= 0 && value <= 3, "pcnn_set_option: method must be 0..3");
         index->opt_method = value;
+    } else if (!std::strcmp(name, "profile")) {
+        PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: profile must be 0 or 1");
+        DeviceGuard g(index->device);
+        if (value && !index->prof0) {
+            PCNN_CUDA(cudaEventCreate(&index->prof0));
+            PCNN_CUDA(cudaEventCreate(&index->prof1));
+        }
+        index->opt_profile = value;
     } else if (!std::strcmp(name, "leaf_log")) {
         PCNN_CHECK_ARG(value >= 0 && value <= 6, "pcnn_set_option: leaf_log must be 0..6");
         index->opt_leaf_log = value;

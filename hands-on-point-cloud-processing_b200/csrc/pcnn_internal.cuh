@@ -26,6 +26,8 @@ struct pcnn_index {
     int opt_method = 0;
     int opt_leaf_log = 1;       // thread-per-query leaf = 2^leaf_log groups
     int opt_warp_leaf_log = 2;  // warp-per-query leaf = 32 points
+    int opt_profile = 0;
+    cudaEvent_t prof0 = nullptr, prof1 = nullptr;  // bracket the last main search kernel
 };
 
 namespace pcnn {
@@ -81,6 +83,14 @@ struct Scratch {
         for (int i = 0; i < np; i++) cudaFreeAsync(p[i], s);
     }
 };
+
+// profile brackets: no-ops unless option "profile" is set
+inline void prof_begin(const pcnn_index* ix, cudaStream_t s) {
+    if (ix->opt_profile && ix->prof0) cudaEventRecord(ix->prof0, s);
+}
+inline void prof_end(const pcnn_index* ix, cudaStream_t s) {
+    if (ix->opt_profile && ix->prof1) cudaEventRecord(ix->prof1, s);
+}
 
 // kernels / launchers implemented across the .cu files
 int launch_knn(const pcnn_index* ix, const float* q, int64_t nq, int stride, int k, int32_t* out_idx,

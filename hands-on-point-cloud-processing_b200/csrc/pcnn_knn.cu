@@ -304,17 +304,21 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }
+        prof_begin(ix, s);
         if (k <= 1) launch_thread_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 2) launch_thread_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 4) launch_thread_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 8) launch_thread_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else launch_thread_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        prof_end(ix, s);
     } else if (method == 3) {
+        prof_begin(ix, s);
         if (k <= 1) launch_brute_k<1>(ix, q, nq, stride, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 2) launch_brute_k<2>(ix, q, nq, stride, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 4) launch_brute_k<4>(ix, q, nq, stride, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 8) launch_brute_k<8>(ix, q, nq, stride, k, out_idx, out_dist, out_dist64, s);
         else launch_brute_k<16>(ix, q, nq, stride, k, out_idx, out_dist, out_dist64, s);
+        prof_end(ix, s);
     } else {
         Scratch sc(s);
         double* lower_key = nullptr;
@@ -324,11 +328,13 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
             PCNN_CUDA(sc.get(&lower_idx, (size_t)nq));
         }
         const WarpPlan wp = make_warp_plan(ix->view);
+        prof_begin(ix, s);
         for (int col0 = 0; col0 < k; col0 += 32) {
             const int kk = (k - col0) < 32 ? (k - col0) : 32;
             knn_warp_kernel<<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
                 ix->view, wp, q, nq, stride, k, col0, kk, lower_key, lower_idx, out_idx, out_dist, out_dist64);
         }
+        prof_end(ix, s);
     }
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;

@@ -194,8 +194,10 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
     const double thr = radius_threshold(radius);
     // counts are written into offsets[1..nq] then scanned in place into offsets[0..nq]
     long long* counts = (long long*)out_offsets + 1;
+    prof_begin(ix, s);
     radius_warp_kernel<false><<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
         ix->view, wp, q, nq, stride, thr, counts, nullptr, nullptr, nullptr, nullptr);
+    prof_end(ix, s);
     Scratch sc(s);
     long long* tmp;
     PCNN_CUDA(sc.get(&tmp, (size_t)nq + 1));
@@ -212,8 +214,10 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
     if (nq == 0) return PCNN_OK;
     const WarpPlan wp = make_warp_plan(ix->view);
     const double thr = radius_threshold(radius);
+    prof_begin(ix, s);
     radius_warp_kernel<true><<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
         ix->view, wp, q, nq, stride, thr, nullptr, (const long long*)offsets, out_idx, out_dist, out_dist64);
+    prof_end(ix, s);
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
 }

@@ -122,6 +122,10 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
  * `method`: 0 = auto, 1 = thread-per-query traversal, 2 = warp-per-query traversal,
  * 3 = brute-force tiles.  Returns PCNN_ERR_INVALID for unknown values. */
 int pcnn_set_option(pcnn_index* index, const char* name, int value);
+/* With option "profile" = 1 every pcnn_knn / pcnn_radius_* call on this handle brackets its
+ * main search kernel (not the query ordering) with CUDA events on the call's stream;
+ * this returns the device time of the most recent one in milliseconds (waits for it). */
+int pcnn_get_profile(const pcnn_index* index, float* main_kernel_ms);
 
 /* ------------------------------------------------------------------ radius search
  * Replaces, for nq queries at once, benchmark.hpp:68-71:

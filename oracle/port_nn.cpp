@@ -99,9 +99,17 @@ struct KdPort {
             double median = vals[m];
             std::vector<int> L, R;
             for (int i : idx) (coord(pts[i], axis) <= median ? L : R).push_back(i);
-            if (R.empty()) {
-                // > leaf_size points identical on this axis' tail: the reference recurses
-                // forever here.  The port stops instead; never hit by tests.
+            bool all_same = R.empty();
+            if (all_same) {
+                const P3& f = pts[idx[0]];
+                for (int i : idx)
+                    if (pts[i].x != f.x || pts[i].y != f.y || pts[i].z != f.z) { all_same = false; break; }
+            }
+            if (all_same) {
+                // > leaf_size coincident points: the reference recurses forever here
+                // (SURVEY 3.1).  The port stops instead; never hit by tests.  (An empty right
+                // side alone is NOT this case: the reference then makes an empty right leaf
+                // and keeps splitting the left side on the next axis, and so does the port.)
                 nodes[me].begin = (int)leaf_pool.size();
                 leaf_pool.insert(leaf_pool.end(), idx.begin(), idx.end());
                 nodes[me].end = (int)leaf_pool.size();

@@ -1,0 +1,170 @@
+"""GPU tests: fused ICP against the restated loop (oracle/icp_loop.hpp), and size-independent
+properties of kNN / radius search at BASELINE.json's full sizes (1M x 1M)."""
+import numpy as np
+import pytest
+
+import parity
+import pcnn_b200 as pc
+
+pytestmark = pytest.mark.gpu
+
+POSE_TOL = 1e-5  # north_star: rotation / translation within 1e-5 after a fixed iteration count
+
+
+@pytest.fixture(scope="module")
+def pair():
+    return pc.synth.icp_pair(20000, seed=pc.synth.BASE_SEED + 3)
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_icp_matches_restated_loop(pair, oracle_port, mode):
+    src, tar, nrm, T = pair
+    ix = pc.Index(tar)
+    got = ix.icp(src, tar_normals=nrm, max_iter=30, max_corres_dist=1.0, loss_epsilon=0.0, mode=mode)
+    want = oracle_port.icp(src, tar, nrm, max_iter=30, max_corres_dist=1.0, loss_epsilon=0.0, mode=mode,
+                           accum=1, nthreads=8)
+    assert got["status"] == 0 and got["iters"] == 30 and got["converged"] == 0
+    assert got["pairs"] == want["pairs"]
+    assert parity.rot_err(got["T"], want["T"]) < POSE_TOL, (got["T"], want["T"])
+    assert parity.trans_err(got["T"], want["T"]) < POSE_TOL
+    # and the float32-as-written variant of the restatement (attribution of drift)
+    want32 = oracle_port.icp(src, tar, nrm, max_iter=30, mode=mode, accum=0, nthreads=8)
+    assert parity.rot_err(got["T"], want32["T"]) < POSE_TOL and parity.trans_err(got["T"], want32["T"]) < 5 * POSE_TOL
+    # known-transform recovery (bounded by the 2 cm range noise, not by arithmetic)
+    assert parity.rot_err(got["T"], T) < (2e-4 if mode == 0 else 2e-3)
+    assert parity.trans_err(got["T"], T) < (2e-3 if mode == 0 else 2e-2)
+    ix.close()
+
+
+def test_icp_iteration_by_iteration(pair, oracle_port):
+    # poses after 1, 2, 5 iterations agree too (not just the fixed point)
+    src, tar, nrm, T = pair
+    ix = pc.Index(tar)
+    for it in (1, 2, 5):
+        for mode in (0, 1):
+            got = ix.icp(src, tar_normals=nrm, max_iter=it, mode=mode)
+            want = oracle_port.icp(src, tar, nrm, max_iter=it, mode=mode, accum=1, nthreads=8)
+            assert got["iters"] == it and got["pairs"] == want["pairs"]
+            assert parity.rot_err(got["T"], want["T"]) < POSE_TOL and parity.trans_err(got["T"], want["T"]) < POSE_TOL
+    ix.close()
+
+
+def test_icp_initial_pose_gate_and_convergence_rule(pair, oracle_port):
+    src, tar, nrm, T = pair
+    ix = pc.Index(tar)
+    T0 = np.eye(4, dtype=np.float32)
+    T0[:3, :3] = pc.synth.rot_zx(1.0, 0.0)
+    T0[:3, 3] = (0.1, 0.0, 0.0)
+    for kw in (dict(init_T=T0, max_corres_dist=0.25), dict(max_corres_dist=0.04), dict(loss_epsilon=1e30, max_iter=100)):
+        args = dict(max_iter=12, max_corres_dist=1.0, loss_epsilon=0.0, mode=0)
+        args.update(kw)
+        got = ix.icp(src, tar_normals=nrm, **args)
+        want = oracle_port.icp(src, tar, nrm, accum=1, nthreads=8, **args)
+        assert (got["iters"], got["converged"], got["status"], got["pairs"]) == \
+               (want["iters"], want["converged"], want["status"], want["pairs"]), (kw, got, want)
+        assert parity.rot_err(got["T"], want["T"]) < POSE_TOL and parity.trans_err(got["T"], want["T"]) < POSE_TOL
+    # gate so tight that nothing matches: status 1, pose unchanged
+    got = ix.icp(src + 50.0, max_iter=5, max_corres_dist=1e-12, mode=0)
+    assert got["status"] == 1 and got["iters"] == 0 and np.array_equal(got["T"], np.eye(4, dtype=np.float32))
+    ix.close()
+
+
+def test_icp_split_phase_equals_fused(pair):
+    import torch
+    src, tar, nrm, T = pair
+    ix = pc.Index(tar)
+    fused = ix.icp(src, tar_normals=nrm, max_iter=10, mode=1)
+    dn = torch.from_numpy(nrm).cuda()
+    st = pc.IcpState(ix, torch.from_numpy(src).cuda(), tar_normals=dn, max_iter=10, mode=1)
+    for _ in range(10):
+        st.accumulate()
+        st.update()
+    split = st.finish()
+    st.close()
+    assert np.array_equal(split["T"], fused["T"]) and split["pairs"] == fused["pairs"]
+    # two shards of the source, sums added by hand = what an all-reduce does
+    half = len(src) // 2
+    a = pc.IcpState(ix, torch.from_numpy(src[:half]).cuda(), tar_normals=dn, max_iter=10, mode=0)
+    b = pc.IcpState(ix, torch.from_numpy(src[half:]).cuda(), tar_normals=dn, max_iter=10, mode=0, src_index_base=half)
+    for _ in range(10):
+        a.accumulate()
+        b.accumulate()
+        tot = a.sums[:31] + b.sums[:31]
+        last = torch.maximum(a.sums[31:].view(torch.int64), b.sums[31:].view(torch.int64))
+        for s in (a, b):
+            s.sums[:31] = tot
+            s.sums[31:].view(torch.int64).copy_(last)
+            s.update()
+    ra, rb = a.finish(), b.finish()
+    one = ix.icp(src, max_iter=10, mode=0)
+    assert np.array_equal(ra["T"], rb["T"]) and ra["pairs"] == one["pairs"]
+    assert parity.rot_err(ra["T"], one["T"]) < 1e-6 and parity.trans_err(ra["T"], one["T"]) < 1e-6
+    a.close(); b.close(); ix.close()
+
+
+# ---------------------------------------------------------------- full-size properties
+@pytest.fixture(scope="module")
+def big():
+    pts, _ = pc.synth.aggregate(1_000_000, 9, seed=pc.synth.BASE_SEED + 2)
+    qry, _ = pc.synth.aggregate(1_000_000, 9, seed=pc.synth.BASE_SEED + 2, lateral=1.0, noise_seed=77)
+    return pts, qry
+
+
+def test_full_size_knn_properties(big, oracle_port):
+    import torch
+    pts, qry = big
+    ix = pc.Index(pts)
+    dq = torch.from_numpy(pts).cuda()
+    idx, dist = ix.knn(dq, 8, dist="f64")
+    torch.cuda.synchronize()
+    idx, dist = idx.cpu().numpy(), dist.cpu().numpy()
+    # self-query: every point finds itself at distance 0 first (points are unique)
+    assert np.array_equal(idx[:, 0], np.arange(len(pts), dtype=np.int32)) and (dist[:, 0] == 0).all()
+    assert (np.diff(dist, axis=1) >= 0).all()                       # rows ascending
+    assert (idx >= 0).all() and (idx < len(pts)).all()
+    assert (np.sort(idx, axis=1)[:, 1:] != np.sort(idx, axis=1)[:, :-1]).all()  # no duplicates in a row
+    # distances are what the indices say (checksum of the whole output, exact)
+    assert np.array_equal(np.sqrt(parity.ref_d2(pts, pts, idx)), dist)
+    # sampled rows against the canonical brute force, in-cloud and off-cloud queries
+    sel = np.arange(0, len(pts), 2003)
+    cidx, cd2 = oracle_port.brute_knn(pts, pts[sel], 8, nthreads=8)
+    parity.assert_knn_equals_canonical(idx[sel], dist[sel], cidx, cd2)
+    qi, qd = ix.knn(qry, 8, dist="f64")                              # host entry, pipelined chunks
+    cidx, cd2 = oracle_port.brute_knn(pts, qry[sel], 8, nthreads=8)
+    parity.assert_knn_equals_canonical(qi[sel], qd[sel], cidx, cd2)
+    # query order does not matter
+    ix.set_option("sort_queries", 0)
+    qi2, qd2 = ix.knn(qry[:200000], 8, dist="f64")
+    assert np.array_equal(qi2, qi[:200000]) and np.array_equal(qd2, qd[:200000])
+    ix.close()
+
+
+def test_full_size_radius_properties(big, oracle_port):
+    import torch
+    pts, qry = big
+    ix = pc.Index(pts, kind=pc.OCTREE, leaf_size=32, min_extent=1e-4)
+    nq = 200_000
+    dq = torch.from_numpy(qry[:nq]).cuda()
+    off, idx, dist = ix.radius(dq, 0.5, dist="f64")
+    torch.cuda.synchronize()
+    off, idx, dist = off.cpu().numpy(), idx.cpu().numpy(), dist.cpu().numpy()
+    assert off[0] == 0 and (np.diff(off) >= 0).all() and off[-1] == len(idx)
+    assert (dist <= 0.5).all() and (idx >= 0).all() and (idx < len(pts)).all()
+    row = np.repeat(np.arange(nq), np.diff(off))
+    assert np.array_equal(np.sqrt(parity.ref_d2(pts, qry[row], idx)), dist)   # every hit is real
+    # monotone in r, and consistent with kNN: hits(r) = #{kNN distances <= r} when that is < k
+    off2, _, _ = ix.radius(dq, 0.25, dist=None)
+    assert (np.diff(off2.cpu().numpy()) <= np.diff(off)).all()
+    ki, kd = ix.knn(dq[:20000], 64, dist="f64")
+    cnt = (kd.cpu().numpy() <= 0.5).sum(axis=1)
+    full = cnt < 64
+    assert np.array_equal(np.diff(off)[:20000][full], cnt[full])
+    # sampled rows against the reference-order oracle (as sets)
+    t = oracle_port.build(1, pts, 32, 1e-4)
+    sel = np.arange(0, nq, 397)
+    roff, ridx, rdist = t.radius(qry[sel], 0.5, nthreads=8)
+    sub_rows = [np.arange(off[s], off[s + 1]) for s in sel]
+    sub_off = np.concatenate([[0], np.cumsum([len(r) for r in sub_rows])])
+    cat = np.concatenate(sub_rows) if len(sub_rows) else np.zeros(0, np.int64)
+    parity.assert_radius_matches_reference(sub_off, idx[cat], dist[cat], roff, ridx, rdist)
+    ix.close()

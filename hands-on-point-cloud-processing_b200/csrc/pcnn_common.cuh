@@ -13,6 +13,7 @@
 // SAME operation sequence so that, by monotonicity of rounding, bound <= d2 of every point
 // inside the box: pruning on `bound > worst` can never lose a neighbour or a tie.
 #pragma once
+#include <cmath>
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -115,6 +116,57 @@ PCNN_HD float boxlb32(const float4& lo, const float4& hi, float qx, float qy, fl
     float dy = fmax0(lo.y - qy, qy - hi.y);
     float dz = fmax0(lo.z - qz, qz - hi.z);
     return fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz));
+}
+
+#if !defined(__CUDA_ARCH__)
+inline float i2f_host_prev(float f) { return nextafterf(f, -HUGE_VALF); }
+inline float i2f_host_next(float f) { return nextafterf(f, HUGE_VALF); }
+#endif
+
+// ---- conservative float32 filters in front of the exact double key
+// lbsq32() returns a float that is <= (1 - 2^-20) * (ax^2 + ay^2 + az^2) in real arithmetic for
+// non-negative inputs that are themselves lower bounds of |dx|, |dy|, |dz|.  The exact key of
+// any point is >= that real value * (1 - 2^-50), so `lbsq32 > ru32(worst)` proves the point
+// (or every point of the box) cannot enter the list -- ties included.  Cheap: FP32 pipe only.
+PCNN_HD float lbsq32(float ax, float ay, float az) {
+#if defined(__CUDA_ARCH__)
+    const float s = __fadd_rd(__fadd_rd(__fmul_rd(ax, ax), __fmul_rd(ay, ay)), __fmul_rd(az, az));
+    return __fmul_rd(s, 0.99999905f);
+#else
+    const double s = (double)ax * ax + (double)ay * ay + (double)az * az;
+    return (float)(s * 0.9999980926513672);  // extra margin covers the host's round-to-nearest
+#endif
+}
+// |a - b| rounded toward zero (never above the real difference)
+PCNN_HD float absdiff_rz(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return fabsf(__fsub_rz(a, b));
+#else
+    const double d = (double)a - (double)b;
+    float f = (float)(d < 0 ? -d : d);
+    if ((double)f > (d < 0 ? -d : d)) f = i2f_host_prev(f);
+    return f;
+#endif
+}
+// max(lo - q, q - hi, 0) with the differences rounded down
+PCNN_HD float boxgap_rd(float lo, float hi, float q) {
+#if defined(__CUDA_ARCH__)
+    return fmaxf(fmaxf(__fsub_rd(lo, q), __fsub_rd(q, hi)), 0.0f);
+#else
+    const float a = absdiff_rz(lo, q), b = absdiff_rz(q, hi);
+    const float m = lo > q ? a : (q > hi ? b : 0.0f);
+    return m;
+#endif
+}
+// smallest float >= w
+PCNN_HD float ru32(double w) {
+#if defined(__CUDA_ARCH__)
+    return __double2float_ru(w);
+#else
+    float f = (float)w;
+    if ((double)f < w) f = i2f_host_next(f);
+    return f;
+#endif
 }
 
 // ---- Morton codes

@@ -17,6 +17,16 @@
 
 namespace pcnn {
 
+// host-only work counters for tests/hostsim (algorithmic cost studies); no-ops in the product
+#if defined(PCNN_HOST_COUNTERS) && !defined(__CUDACC__)
+extern thread_local long g_cnt_box, g_cnt_pt;
+#define PCNN_COUNT_BOX() (++pcnn::g_cnt_box)
+#define PCNN_COUNT_PT() (++pcnn::g_cnt_pt)
+#else
+#define PCNN_COUNT_BOX() ((void)0)
+#define PCNN_COUNT_PT() ((void)0)
+#endif
+
 #define PCNN_INF_D (__longlong_as_double_compat(0x7ff0000000000000LL))
 
 PCNN_HD double __longlong_as_double_compat(long long v) {
@@ -94,22 +104,56 @@ PCNN_HD int home_group(const IndexView& iv, unsigned long long qc) {
     return lo > 0 ? lo - 1 : 0;
 }
 
+// first g with gcode[g] >= qc, minus one (clamped to 0): every group before it holds only
+// codes < qc
+PCNN_HD int group_before(const IndexView& iv, unsigned long long qc) {
+    int lo = 0, hi = iv.n0;
+    while (lo < hi) {
+        int mid = (lo + hi) >> 1;
+#if defined(__CUDA_ARCH__)
+        unsigned long long c = __ldg(iv.gcode + mid);
+#else
+        unsigned long long c = iv.gcode[mid];
+#endif
+        if (c < qc) lo = mid + 1; else hi = mid;
+    }
+    return lo > 0 ? lo - 1 : 0;
+}
+
+// Scan one 8-point group.  A float32 lower bound of d2 rejects most candidates on the FP32
+// pipe; only survivors pay for the exact double key.  wf = ru32(tk.worst()) is kept current.
 template <int K>
-PCNN_HD void scan_group64(const IndexView& iv, int g, double qx, double qy, double qz, TopK<K>& tk) {
+PCNN_HD void scan_group64(const IndexView& iv, int g, float qxf, float qyf, float qzf, double qx,
+                          double qy, double qz, TopK<K>& tk, float& wf) {
     const int first = g << PCNN_GROUP_LOG;
     const int cnt = (iv.n - first) < PCNN_GROUP ? (iv.n - first) : PCNN_GROUP;
 #pragma unroll
     for (int j = 0; j < PCNN_GROUP; j++) {
         if (j < cnt) {
-            float4 p = ldpt(iv.pts + first + j);
-            double d = key64(p.x, p.y, p.z, qx, qy, qz);
-            int id = f2i(p.w);
-            if (d <= tk.worst() && tk.accepts(d, id)) tk.insert(d, id);
+            const float4 p = ldpt(iv.pts + first + j);
+            PCNN_COUNT_PT();
+            const float lbf = lbsq32(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
+            if (!(lbf > wf)) {
+                const double d = key64(p.x, p.y, p.z, qx, qy, qz);
+                const int id = f2i(p.w);
+                if (d <= tk.worst() && tk.accepts(d, id)) {
+                    tk.insert(d, id);
+                    wf = ru32(tk.worst());
+                }
+            }
         }
     }
 }
 
 // kNN of one query; leaf_log = log2(groups per leaf), 0 <= leaf_log < nlev.
+//  1. home scan: the group holding the query's Morton code and its two neighbours seed the
+//     k-th distance bound r;
+//  2. Morton window: every point within r of q lies componentwise inside [q-r, q+r], and the
+//     Morton code is monotone in each coordinate, so its code lies in [code(q-r), code(q+r)]:
+//     two binary searches turn that into a group range [g_lo, g_hi] and the sweep never
+//     looks outside it (no walk down from the root);
+//  3. stackless sweep of that range: float32 conservative box tests prune subtrees
+//     (i = (node+1) << l), leaves are scanned with the exact double key.
 template <int K>
 PCNN_HD void knn_thread(const IndexView& iv, float qxf, float qyf, float qzf, int leaf_log,
                         TopK<K>& tk) {
@@ -118,31 +162,60 @@ PCNN_HD void knn_thread(const IndexView& iv, float qxf, float qyf, float qzf, in
     const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
     const int h = home_group(iv, morton63(qxf, qyf, qzf, iv.cube, iv.cube[3]));
     const int h0 = h > 0 ? h - 1 : 0, h1 = (h + 1 < iv.n0) ? h + 1 : iv.n0 - 1;
-    for (int g = h0; g <= h1; g++) scan_group64<K>(iv, g, qx, qy, qz, tk);
+    float wf = i2f(0x7f800000);
+    for (int g = h0; g <= h1; g++) scan_group64<K>(iv, g, qxf, qyf, qzf, qx, qy, qz, tk, wf);
 
     const int top = iv.nlev - 1;
     if (leaf_log > top) leaf_log = top;
-    int i = 0, l = top;
-    while (i < iv.n0) {
-        const int node = i >> l;
-        const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + node);
-        const float4 lo = ldpt(b), hi = ldpt(b + 1);
-        const double lb = boxlb64(lo, hi, qx, qy, qz);
-        if (lb > tk.worst()) {                // nothing inside can enter (ties included)
-            i = (node + 1) << l;
-        } else if (l > leaf_log) {
-            l -= 1;                           // test the left child next (same i)
-            continue;
-        } else {
-            const int g0 = node << l;
-            int g1 = (node + 1) << l;
-            if (g1 > iv.n0) g1 = iv.n0;
-            for (int g = g0; g < g1; g++)
-                if (g < h0 || g > h1) scan_group64<K>(iv, g, qx, qy, qz, tk);
-            i = g1 >= iv.n0 ? iv.n0 : (node + 1) << l;
+    int g_lo = 0, g_hi = iv.n0 - 1;
+    if (wf < 3.0e38f) {
+        // r >= sqrt(worst): float sqrt of an upper bound, nudged up
+#if defined(__CUDA_ARCH__)
+        const float r = __fmul_ru(__fsqrt_ru(wf), 1.000001f);
+        const float lx = __fsub_rd(qxf, r), ly = __fsub_rd(qyf, r), lz = __fsub_rd(qzf, r);
+        const float hx = __fadd_ru(qxf, r), hy = __fadd_ru(qyf, r), hz = __fadd_ru(qzf, r);
+#else
+        const float r = (float)(std::sqrt((double)wf) * 1.000002);
+        const float lx = i2f_host_prev(qxf - r), ly = i2f_host_prev(qyf - r), lz = i2f_host_prev(qzf - r);
+        const float hx = i2f_host_next(qxf + r), hy = i2f_host_next(qyf + r), hz = i2f_host_next(qzf + r);
+#endif
+        g_lo = group_before(iv, morton63(lx, ly, lz, iv.cube, iv.cube[3]));
+        g_hi = home_group(iv, morton63(hx, hy, hz, iv.cube, iv.cube[3]));
+    }
+    int i = g_lo;
+    int l = i == 0 ? top : ctz32((unsigned)i);
+    if (l > top) l = top;
+    while (i <= g_hi) {
+        // phase A: walk box tests until a leaf must be scanned
+        int leaf = -1;
+        while (i <= g_hi) {
+            const int node = i >> l;
+            const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + node);
+            const float4 lo = ldpt(b), hi = ldpt(b + 1);
+            PCNN_COUNT_BOX();
+            const float lbf = lbsq32(boxgap_rd(lo.x, hi.x, qxf), boxgap_rd(lo.y, hi.y, qyf),
+                                     boxgap_rd(lo.z, hi.z, qzf));
+            if (lbf > wf) {                       // nothing inside can enter (ties included)
+                i = (node + 1) << l;
+                const int a = ctz32((unsigned)i); // highest level whose node starts at i
+                l = a < top ? a : top;
+            } else if (l > leaf_log) {
+                l -= 1;                           // test the left child next (same i)
+            } else {
+                leaf = node;
+                break;
+            }
         }
+        if (leaf < 0) break;
+        // phase B: scan the leaf
+        const int g0 = leaf << l;
+        int g1 = (leaf + 1) << l;
+        if (g1 > iv.n0) g1 = iv.n0;
+        for (int g = g0; g < g1; g++)
+            if (g < h0 || g > h1) scan_group64<K>(iv, g, qxf, qyf, qzf, qx, qy, qz, tk, wf);
+        i = g1;
         if (i >= iv.n0) break;
-        const int a = ctz32((unsigned)i);     // highest level whose node starts at i
+        const int a = ctz32((unsigned)i);
         l = a < top ? a : top;
     }
 }

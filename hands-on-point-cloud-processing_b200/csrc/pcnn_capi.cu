@@ -8,23 +8,58 @@
 
 using namespace pcnn;
 
+// Streams and device staging buffers of the host-pointer entry points; one per index handle,
+// created on first use, grown on demand, freed with the handle.
+constexpr int HOST_STREAMS = 3;
+struct HostPipe {
+    cudaStream_t s[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+    pcnn::DevBuf q[HOST_STREAMS], idx[HOST_STREAMS], d32[HOST_STREAMS], d64[HOST_STREAMS];
+    pcnn::DevBuf off;  // radius: CSR offsets
+    cudaEvent_t ev[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+};
+
+namespace pcnn {
+void free_host_pipe(HostPipe* hp) {
+    if (!hp) return;
+    for (int i = 0; i < HOST_STREAMS; i++) {
+        if (hp->s[i]) { cudaStreamSynchronize(hp->s[i]); cudaStreamDestroy(hp->s[i]); }
+        if (hp->ev[i]) cudaEventDestroy(hp->ev[i]);
+        hp->q[i].release(); hp->idx[i].release(); hp->d32[i].release(); hp->d64[i].release();
+    }
+    hp->off.release();
+    delete hp;
+}
+}  // namespace pcnn
+
 namespace {
 
-constexpr int64_t HOST_CHUNK = 1 << 18;  // queries per pipeline stage
-constexpr int HOST_STREAMS = 3;
+// pipeline stage size: enough stages to hide the PCIe copies behind the kernels, few enough
+// that the ~14 launches per stage stay negligible
+int64_t host_chunk(int64_t nq) {
+    int64_t c = (nq + 7) / 8;
+    c = std::max<int64_t>(c, 1 << 16);
+    c = std::min<int64_t>(c, 1 << 18);
+    return std::min(c, nq);
+}
 
-struct StreamSet {
-    cudaStream_t s[HOST_STREAMS] = {nullptr, nullptr, nullptr};
-    bool ok = true;
-    StreamSet() {
-        for (int i = 0; i < HOST_STREAMS; i++)
-            if (cudaStreamCreateWithFlags(&s[i], cudaStreamNonBlocking) != cudaSuccess) ok = false;
+// caller holds index->pipe_mu
+int get_pipe(pcnn_index* ix, HostPipe** out, const char* fn) {
+    if (!ix->pipe) {
+        HostPipe* hp = new (std::nothrow) HostPipe;
+        if (!hp) { set_error("%s: host allocation failed", fn); return PCNN_ERR_NOMEM; }
+        for (int i = 0; i < HOST_STREAMS; i++) {
+            if (cudaStreamCreateWithFlags(&hp->s[i], cudaStreamNonBlocking) != cudaSuccess ||
+                cudaEventCreateWithFlags(&hp->ev[i], cudaEventDisableTiming) != cudaSuccess) {
+                set_error("%s: stream creation failed: %s", fn, cudaGetErrorString(cudaGetLastError()));
+                free_host_pipe(hp);
+                return PCNN_ERR_CUDA;
+            }
+        }
+        ix->pipe = hp;
     }
-    ~StreamSet() {
-        for (int i = 0; i < HOST_STREAMS; i++)
-            if (s[i]) cudaStreamDestroy(s[i]);
-    }
-};
+    *out = ix->pipe;
+    return PCNN_OK;
+}
 
 int check_query_args(const char* fn, const pcnn_index* index, const float* q, int64_t nq, int stride) {
     PCNN_CHECK_ARG(index != nullptr, "%s: index is NULL", fn);
@@ -61,50 +96,51 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
     if (nq == 0) return PCNN_OK;
     DeviceGuard g(index->device);
     if (!g.ok) { set_error("pcnn_knn_host: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
-    StreamSet ss;
-    if (!ss.ok) { set_error("pcnn_knn_host: stream creation failed"); return PCNN_ERR_CUDA; }
-    const int64_t chunk = std::min<int64_t>(HOST_CHUNK, nq);
-    // per-stream staging buffers, reused round-robin (stream order protects the reuse)
-    float* dq[HOST_STREAMS] = {nullptr, nullptr, nullptr};
-    int32_t* di[HOST_STREAMS] = {nullptr, nullptr, nullptr};
-    float* dd[HOST_STREAMS] = {nullptr, nullptr, nullptr};
-    double* dd64[HOST_STREAMS] = {nullptr, nullptr, nullptr};
-    cudaError_t e = cudaSuccess;
+    pcnn_index* ix = const_cast<pcnn_index*>(index);
+    std::lock_guard<std::mutex> lk(ix->pipe_mu);
+    HostPipe* hp = nullptr;
+    rc = get_pipe(ix, &hp, "pcnn_knn_host");
+    if (rc != PCNN_OK) return rc;
+    const int64_t chunk = host_chunk(nq);
     const int nstreams = (int)std::min<int64_t>(HOST_STREAMS, (nq + chunk - 1) / chunk);
+    cudaError_t e = cudaSuccess;
     for (int i = 0; i < nstreams && e == cudaSuccess; i++) {
-        e = cudaMalloc(&dq[i], sizeof(float) * (size_t)chunk * stride);
-        if (e == cudaSuccess) e = cudaMalloc(&di[i], sizeof(int32_t) * (size_t)chunk * k);
-        if (e == cudaSuccess && out_dist_host) e = cudaMalloc(&dd[i], sizeof(float) * (size_t)chunk * k);
-        if (e == cudaSuccess && out_dist64_host) e = cudaMalloc(&dd64[i], sizeof(double) * (size_t)chunk * k);
+        e = hp->q[i].ensure(sizeof(float) * (size_t)chunk * stride);
+        if (e == cudaSuccess) e = hp->idx[i].ensure(sizeof(int32_t) * (size_t)chunk * k);
+        if (e == cudaSuccess && out_dist_host) e = hp->d32[i].ensure(sizeof(float) * (size_t)chunk * k);
+        if (e == cudaSuccess && out_dist64_host) e = hp->d64[i].ensure(sizeof(double) * (size_t)chunk * k);
     }
     if (e != cudaSuccess) {
         set_error("pcnn_knn_host: staging allocation failed: %s", cudaGetErrorString(e));
-        rc = PCNN_ERR_NOMEM;
+        return PCNN_ERR_NOMEM;
     }
     int c = 0;
     for (int64_t q0 = 0; q0 < nq && rc == PCNN_OK; q0 += chunk, c++) {
         const int b = c % nstreams;
         const int64_t m = std::min<int64_t>(chunk, nq - q0);
-        cudaStream_t s = ss.s[b];
-        e = cudaMemcpyAsync(dq[b], q_host + q0 * stride, sizeof(float) * (size_t)m * stride, cudaMemcpyHostToDevice, s);
+        cudaStream_t s = hp->s[b];
+        float* dq = (float*)hp->q[b].p;
+        int32_t* di = (int32_t*)hp->idx[b].p;
+        float* dd = out_dist_host ? (float*)hp->d32[b].p : nullptr;
+        double* dd64 = out_dist64_host ? (double*)hp->d64[b].p : nullptr;
+        e = cudaMemcpyAsync(dq, q_host + q0 * stride, sizeof(float) * (size_t)m * stride, cudaMemcpyHostToDevice, s);
         if (e != cudaSuccess) { set_error("pcnn_knn_host: H2D failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; break; }
-        rc = launch_knn(index, dq[b], m, stride, k, di[b], dd[b], dd64[b], s);
+        rc = launch_knn(index, dq, m, stride, k, di, dd, dd64, s);
         if (rc != PCNN_OK) break;
-        e = cudaMemcpyAsync(out_idx_host + q0 * k, di[b], sizeof(int32_t) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
+        e = cudaMemcpyAsync(out_idx_host + q0 * k, di, sizeof(int32_t) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && out_dist_host)
-            e = cudaMemcpyAsync(out_dist_host + q0 * k, dd[b], sizeof(float) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
+            e = cudaMemcpyAsync(out_dist_host + q0 * k, dd, sizeof(float) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && out_dist64_host)
-            e = cudaMemcpyAsync(out_dist64_host + q0 * k, dd64[b], sizeof(double) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
+            e = cudaMemcpyAsync(out_dist64_host + q0 * k, dd64, sizeof(double) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
         if (e != cudaSuccess) { set_error("pcnn_knn_host: D2H failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; }
     }
-    for (int i = 0; i < HOST_STREAMS; i++) {
-        e = cudaStreamSynchronize(ss.s[i]);
+    for (int i = 0; i < nstreams; i++) {
+        e = cudaStreamSynchronize(hp->s[i]);
         if (e != cudaSuccess && rc == PCNN_OK) {
             set_error("pcnn_knn_host: device work failed: %s", cudaGetErrorString(e));
             rc = PCNN_ERR_CUDA;
         }
     }
-    for (int i = 0; i < HOST_STREAMS; i++) { cudaFree(dq[i]); cudaFree(di[i]); cudaFree(dd[i]); cudaFree(dd64[i]); }
     return rc;
 }
 
@@ -151,19 +187,20 @@ int pcnn_radius_host(const pcnn_index* index, const float* q_host, int64_t nq, i
     DeviceGuard g(index->device);
     if (!g.ok) { set_error("pcnn_radius_host: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
     if (nq == 0) { offsets_host[0] = 0; return PCNN_OK; }
-    cudaStream_t s = nullptr;
-    PCNN_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-    float* dq = nullptr;
-    int64_t* doff = nullptr;
-    int32_t* di = nullptr;
-    float* dd = nullptr;
-    double* dd64 = nullptr;
-    cudaError_t e = cudaMalloc(&dq, sizeof(float) * (size_t)nq * stride);
-    if (e == cudaSuccess) e = cudaMalloc(&doff, sizeof(int64_t) * ((size_t)nq + 1));
+    pcnn_index* ix = const_cast<pcnn_index*>(index);
+    std::lock_guard<std::mutex> lk(ix->pipe_mu);
+    HostPipe* hp = nullptr;
+    rc = get_pipe(ix, &hp, "pcnn_radius_host");
+    if (rc != PCNN_OK) return rc;
+    cudaStream_t s = hp->s[0], s1 = hp->s[1];
+    cudaError_t e = hp->q[0].ensure(sizeof(float) * (size_t)nq * stride);
+    if (e == cudaSuccess) e = hp->off.ensure(sizeof(int64_t) * ((size_t)nq + 1));
+    float* dq = (float*)hp->q[0].p;
+    int64_t* doff = (int64_t*)hp->off.p;
     if (e == cudaSuccess) e = cudaMemcpyAsync(dq, q_host, sizeof(float) * (size_t)nq * stride, cudaMemcpyHostToDevice, s);
-    if (e != cudaSuccess) { set_error("pcnn_radius_host: staging failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_NOMEM; }
+    if (e != cudaSuccess) { set_error("pcnn_radius_host: staging failed: %s", cudaGetErrorString(e)); return PCNN_ERR_NOMEM; }
     int64_t total = 0;
-    if (rc == PCNN_OK) rc = launch_radius_count(index, dq, nq, stride, radius, doff, s);
+    rc = launch_radius_count(index, dq, nq, stride, radius, doff, s);
     if (rc == PCNN_OK) {
         e = cudaMemcpyAsync(offsets_host, doff, sizeof(int64_t) * ((size_t)nq + 1), cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess) e = cudaStreamSynchronize(s);
@@ -176,24 +213,29 @@ int pcnn_radius_host(const pcnn_index* index, const float* q_host, int64_t nq, i
     }
     if (rc == PCNN_OK && total > 0) {
         PCNN_CHECK_ARG(out_idx_host != nullptr, "pcnn_radius_host: out_idx is NULL");
-        e = cudaMalloc(&di, sizeof(int32_t) * (size_t)total);
-        if (e == cudaSuccess && out_dist_host) e = cudaMalloc(&dd, sizeof(float) * (size_t)total);
-        if (e == cudaSuccess && out_dist64_host) e = cudaMalloc(&dd64, sizeof(double) * (size_t)total);
-        if (e != cudaSuccess) { set_error("pcnn_radius_host: output allocation failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_NOMEM; }
-        if (rc == PCNN_OK) rc = launch_radius_fill(index, dq, nq, stride, radius, doff, di, dd, dd64, s);
+        e = hp->idx[0].ensure(sizeof(int32_t) * (size_t)total);
+        if (e == cudaSuccess && out_dist_host) e = hp->d32[0].ensure(sizeof(float) * (size_t)total);
+        if (e == cudaSuccess && out_dist64_host) e = hp->d64[0].ensure(sizeof(double) * (size_t)total);
+        if (e != cudaSuccess) { set_error("pcnn_radius_host: output allocation failed: %s", cudaGetErrorString(e)); return PCNN_ERR_NOMEM; }
+        int32_t* di = (int32_t*)hp->idx[0].p;
+        float* dd = out_dist_host ? (float*)hp->d32[0].p : nullptr;
+        double* dd64 = out_dist64_host ? (double*)hp->d64[0].p : nullptr;
+        rc = launch_radius_fill(index, dq, nq, stride, radius, doff, di, dd, dd64, s);
         if (rc == PCNN_OK) {
-            e = cudaMemcpyAsync(out_idx_host, di, sizeof(int32_t) * (size_t)total, cudaMemcpyDeviceToHost, s);
+            // the three result arrays leave on two streams so the copies share the link
+            e = cudaEventRecord(hp->ev[0], s);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(out_idx_host, di, sizeof(int32_t) * (size_t)total, cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess && (out_dist_host || out_dist64_host)) e = cudaStreamWaitEvent(s1, hp->ev[0], 0);
             if (e == cudaSuccess && out_dist_host)
-                e = cudaMemcpyAsync(out_dist_host, dd, sizeof(float) * (size_t)total, cudaMemcpyDeviceToHost, s);
+                e = cudaMemcpyAsync(out_dist_host, dd, sizeof(float) * (size_t)total, cudaMemcpyDeviceToHost, s1);
             if (e == cudaSuccess && out_dist64_host)
-                e = cudaMemcpyAsync(out_dist64_host, dd64, sizeof(double) * (size_t)total, cudaMemcpyDeviceToHost, s);
+                e = cudaMemcpyAsync(out_dist64_host, dd64, sizeof(double) * (size_t)total, cudaMemcpyDeviceToHost, s1);
             if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s1);
             if (e != cudaSuccess) { set_error("pcnn_radius_host: fill pass failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; }
         }
     }
     cudaStreamSynchronize(s);
-    cudaFree(dq); cudaFree(doff); cudaFree(di); cudaFree(dd); cudaFree(dd64);
-    cudaStreamDestroy(s);
     return rc;
 }
 

@@ -25,6 +25,33 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 
+// one pool per device, created on first use
+cudaMemPool_t lib_pool() {
+    static std::mutex mu;
+    static cudaMemPool_t pools[64] = {};
+    static bool tried[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!tried[dev]) {
+        tried[dev] = true;
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaMemPool_t pool = nullptr;
+        if (cudaMemPoolCreate(&pool, &props) == cudaSuccess) {
+            unsigned long long keep = ~0ULL;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            pools[dev] = pool;
+        } else {
+            cudaGetLastError();
+        }
+    }
+    return pools[dev];
+}
+
 constexpr int BB_THREADS = 256;
 constexpr int BB_BLOCKS = 592;  // 4 per SM on 148 SMs
 
@@ -141,6 +168,7 @@ __global__ void box_up(const float4* __restrict__ child, int nchild, float4* __r
 
 static void free_index(pcnn_index* ix) {
     if (!ix) return;
+    free_host_pipe(ix->pipe);
     cudaFree(ix->pts);
     cudaFree(ix->gcode);
     cudaFree(ix->box);
@@ -333,6 +361,17 @@ int pcnn_index_get_info(const pcnn_index* index, pcnn_index_info* out) {
     return PCNN_OK;
 }
 
+int pcnn_release_cached(int device) {
+    DeviceGuard g(device);
+    if (!g.ok) { set_error("pcnn_release_cached: cannot select CUDA device %d", device); return PCNN_ERR_CUDA; }
+    cudaMemPool_t pool = lib_pool();
+    if (pool) {
+        PCNN_CUDA(cudaDeviceSynchronize());
+        PCNN_CUDA(cudaMemPoolTrimTo(pool, 0));
+    }
+    return PCNN_OK;
+}
+
 int pcnn_get_profile(const pcnn_index* index, float* main_kernel_ms) {
     PCNN_CHECK_ARG(index && main_kernel_ms, "pcnn_get_profile: NULL argument");
     PCNN_CHECK_ARG(index->opt_profile && index->prof0, "pcnn_get_profile: option \"profile\" is not set");
@@ -348,7 +387,7 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: sort_queries must be 0 or 1");
         index->opt_sort_queries = value;
     } else if (!std::strcmp(name, "method")) {
-        PCNN_CHECK_ARG(value >= 0 && value <= 3, "pcnn_set_option: method must be 0..3");
+        PCNN_CHECK_ARG(value >= 0 && value <= 4, "pcnn_set_option: method must be 0..4");
         index->opt_method = value;
     } else if (!std::strcmp(name, "profile")) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: profile must be 0 or 1");
@@ -361,6 +400,9 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
     } else if (!std::strcmp(name, "leaf_log")) {
         PCNN_CHECK_ARG(value >= 0 && value <= 6, "pcnn_set_option: leaf_log must be 0..6");
         index->opt_leaf_log = value;
+    } else if (!std::strcmp(name, "coherent_leaf_log")) {
+        PCNN_CHECK_ARG(value >= 0 && value <= 6, "pcnn_set_option: coherent_leaf_log must be 0..6");
+        index->opt_coherent_leaf_log = value;
     } else {
         set_error("pcnn_set_option: unknown option '%s'", name);
         return PCNN_ERR_INVALID;

@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include "../../include/pcnn.h"
 #include "pcnn_common.cuh"
@@ -26,8 +27,13 @@ struct pcnn_index {
     int opt_method = 0;
     int opt_leaf_log = 1;       // thread-per-query leaf = 2^leaf_log groups
     int opt_warp_leaf_log = 2;  // warp-per-query leaf = 32 points
+    int opt_coherent_leaf_log = 0;  // warp-coherent traversal: leaf = 2^this groups
     int opt_profile = 0;
     cudaEvent_t prof0 = nullptr, prof1 = nullptr;  // bracket the last main search kernel
+    // staging state of the host-pointer entry points (streams + device buffers), created on
+    // first use and kept for the life of the handle so a call costs no allocation
+    struct HostPipe* pipe = nullptr;
+    std::mutex pipe_mu;
 };
 
 namespace pcnn {
@@ -65,7 +71,12 @@ struct DeviceGuard {
     }
 };
 
-// Stream-ordered scratch allocation that is returned on scope exit.
+// The library's own stream-ordered memory pool on the current device.  Its release threshold
+// is unlimited, so scratch freed by one call is reused by the next instead of going back to
+// the driver at every synchronisation (pcnn_release_cached() trims it).
+cudaMemPool_t lib_pool();
+
+// Stream-ordered scratch allocation that is returned to the pool on scope exit.
 struct Scratch {
     cudaStream_t s;
     void* p[16];
@@ -74,7 +85,9 @@ struct Scratch {
     template <typename T>
     cudaError_t get(T** out, size_t count) {
         void* q = nullptr;
-        cudaError_t e = cudaMallocAsync(&q, count * sizeof(T) + 16, s);
+        cudaMemPool_t pool = lib_pool();
+        cudaError_t e = pool ? cudaMallocFromPoolAsync(&q, count * sizeof(T) + 16, pool, s)
+                             : cudaMallocAsync(&q, count * sizeof(T) + 16, s);
         if (e == cudaSuccess) p[np++] = q;
         *out = (T*)q;
         return e;
@@ -83,6 +96,26 @@ struct Scratch {
         for (int i = 0; i < np; i++) cudaFreeAsync(p[i], s);
     }
 };
+
+// Grow-only device buffer.
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+void free_host_pipe(HostPipe* hp);
 
 // profile brackets: no-ops unless option "profile" is set
 inline void prof_begin(const pcnn_index* ix, cudaStream_t s) {

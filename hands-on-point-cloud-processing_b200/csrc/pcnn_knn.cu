@@ -80,6 +80,123 @@ knn_thread_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     write_row<K>(tk, qi, k, out_idx, out_dist, out_dist64);
 }
 
+// ------------------------------------------------------------------ warp-coherent traversal
+// 32 Morton-consecutive queries share ONE traversal: control flow is warp-uniform (a subtree
+// is skipped only when no lane needs it, decided by a vote), every box and every candidate
+// point is fetched with a single broadcast load, and each lane filters the candidate against
+// its own query and its own k-th distance.  Lanes that pass the float32 filter for some point
+// of a group then run the exact double key + sorted insertion together, one candidate per
+// lane per round, so the expensive part is not serialised lane by lane.  Same result
+// contract as knn_thread(): a lane sees a superset of what its own traversal would visit.
+constexpr int KC_SEED_SPAN = 16;  // widest union of home ranges (groups) scanned by all lanes
+
+template <int K>
+__device__ __forceinline__ void scan_group_shared(const IndexView& iv, int g, bool mine, float qxf, float qyf,
+                                                  float qzf, double qx, double qy, double qz, TopK<K>& tk,
+                                                  float& wf) {
+    const unsigned full = 0xffffffffu;
+    const int first = g << PCNN_GROUP_LOG;
+    const int cnt = (iv.n - first) < PCNN_GROUP ? (iv.n - first) : PCNN_GROUP;  // warp-uniform
+    unsigned pass = 0;
+#pragma unroll
+    for (int j = 0; j < PCNN_GROUP; j++) {
+        if (j < cnt) {
+            const float4 p = __ldg(iv.pts + first + j);  // same address in every lane: one broadcast
+            const float lbf = lbsq32(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
+            if (!(lbf > wf)) pass |= 1u << j;
+        }
+    }
+    if (!mine) pass = 0;
+    while (__any_sync(full, pass != 0)) {
+        if (pass) {
+            const int j = __ffs((int)pass) - 1;
+            pass &= pass - 1;
+            const float4 p = __ldg(iv.pts + first + j);
+            const double d = key64(p.x, p.y, p.z, qx, qy, qz);
+            const int id = __float_as_int(p.w);
+            if (d <= tk.worst() && tk.accepts(d, id)) {
+                tk.insert(d, id);
+                wf = ru32(tk.worst());
+            }
+        }
+    }
+}
+
+template <int K>
+__global__ void __launch_bounds__(KT_THREADS)
+knn_coherent_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
+                    const unsigned* __restrict__ perm, int k, int leaf_log, int32_t* __restrict__ out_idx,
+                    float* __restrict__ out_dist, double* __restrict__ out_dist64) {
+    const unsigned full = 0xffffffffu;
+    const int t = blockIdx.x * KT_THREADS + threadIdx.x;
+    const bool live = t < nq;
+    const int tt = live ? t : nq - 1;  // tail lanes shadow the last query so the warp stays whole
+    const int qi = perm ? (int)perm[tt] : tt;
+    const float* qp = q + (size_t)qi * stride;
+    const float qxf = qp[0], qyf = qp[1], qzf = qp[2];
+    const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
+    TopK<K> tk;
+    tk.init();
+    if (iv.n > 0) {
+        float wf = __int_as_float(0x7f800000);
+        const int h = home_group(iv, morton63(qxf, qyf, qzf, iv.cube, iv.cube[3]));
+        int h0 = h > 0 ? h - 1 : 0, h1 = (h + 1 < iv.n0) ? h + 1 : iv.n0 - 1;
+        const int hmin = __reduce_min_sync(full, h0), hmax = __reduce_max_sync(full, h1);
+        if (hmax - hmin < KC_SEED_SPAN) {
+            // coherent warp: everyone scans the union of the home ranges
+            h0 = hmin;
+            h1 = hmax;
+            for (int g = hmin; g <= hmax; g++)
+                scan_group_shared<K>(iv, g, true, qxf, qyf, qzf, qx, qy, qz, tk, wf);
+        } else {
+            // the curve jumps inside this warp: every lane seeds from its own three groups
+            for (int g = h0; g <= h1; g++) scan_group64<K>(iv, g, qxf, qyf, qzf, qx, qy, qz, tk, wf);
+        }
+        const int top = iv.nlev - 1;
+        if (leaf_log > top) leaf_log = top;
+        int g_lo = 0, g_hi = iv.n0 - 1;
+        if (wf < 3.0e38f) {
+            const float r = __fmul_ru(__fsqrt_ru(wf), 1.000001f);
+            const float lx = __fsub_rd(qxf, r), ly = __fsub_rd(qyf, r), lz = __fsub_rd(qzf, r);
+            const float hx = __fadd_ru(qxf, r), hy = __fadd_ru(qyf, r), hz = __fadd_ru(qzf, r);
+            g_lo = group_before(iv, morton63(lx, ly, lz, iv.cube, iv.cube[3]));
+            g_hi = home_group(iv, morton63(hx, hy, hz, iv.cube, iv.cube[3]));
+        }
+        g_lo = __reduce_min_sync(full, g_lo);
+        g_hi = __reduce_max_sync(full, g_hi);
+        int i = g_lo;
+        int l = i == 0 ? top : min(__ffs(i) - 1, top);
+        while (i <= g_hi) {
+            const int node = i >> l;
+            const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + node);
+            const float4 lo = __ldg(b), hi = __ldg(b + 1);
+            const float lbf = lbsq32(boxgap_rd(lo.x, hi.x, qxf), boxgap_rd(lo.y, hi.y, qyf),
+                                     boxgap_rd(lo.z, hi.z, qzf));
+            const bool need = !(lbf > wf);
+            if (!__any_sync(full, need)) {  // no lane can gain anything in this subtree
+                i = (node + 1) << l;
+                l = min(__ffs(i) - 1, top);
+                continue;
+            }
+            if (l > leaf_log) {
+                l -= 1;
+                continue;
+            }
+            const int g0 = node << l;
+            int g1 = (node + 1) << l;
+            if (g1 > iv.n0) g1 = iv.n0;
+            for (int g = g0; g < g1; g++) {
+                const bool mine = need && (g < h0 || g > h1);
+                if (__any_sync(full, mine)) scan_group_shared<K>(iv, g, mine, qxf, qyf, qzf, qx, qy, qz, tk, wf);
+            }
+            i = g1;
+            if (i >= iv.n0) break;
+            l = min(__ffs(i) - 1, top);
+        }
+    }
+    if (live) write_row<K>(tk, qi, k, out_idx, out_dist, out_dist64);
+}
+
 // ------------------------------------------------------------------ brute-force tiles (TMA)
 constexpr int BF_THREADS = 128;
 constexpr int BF_TILE = 1024;  // points per stage: 16 KB
@@ -283,6 +400,12 @@ static void launch_thread_k(const pcnn_index* ix, const float* q, int nq, int st
         ix->view, q, nq, stride, perm, k, ix->opt_leaf_log, oi, od, od64);
 }
 template <int K>
+static void launch_coherent_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
+                              int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
+    knn_coherent_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
+        ix->view, q, nq, stride, perm, k, ix->opt_coherent_leaf_log, oi, od, od64);
+}
+template <int K>
 static void launch_brute_k(const pcnn_index* ix, const float* q, int nq, int stride, int k, int32_t* oi,
                            float* od, double* od64, cudaStream_t s) {
     knn_brute_kernel<K><<<(nq + BF_THREADS - 1) / BF_THREADS, BF_THREADS, 0, s>>>(
@@ -294,10 +417,24 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     if (nq64 == 0) return PCNN_OK;
     const int nq = (int)nq64;
     int method = ix->opt_method;
-    if (method == 0) method = (k <= 16) ? 1 : 2;
-    if ((method == 1 || method == 3) && k > 16) method = 2;
+    if (method == 0) method = (k <= 16) ? 4 : 2;
+    if ((method == 1 || method == 3 || method == 4) && k > 16) method = 2;
     if (method == 3 && ix->n == 0) method = 1;
-    if (method == 1) {
+    if (method == 4) {
+        Scratch sc(s);
+        unsigned* perm = nullptr;
+        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+            int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+            if (rc != PCNN_OK) return rc;
+        }
+        prof_begin(ix, s);
+        if (k <= 1) launch_coherent_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 2) launch_coherent_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 4) launch_coherent_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 8) launch_coherent_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else launch_coherent_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        prof_end(ix, s);
+    } else if (method == 1) {
         Scratch sc(s);
         unsigned* perm = nullptr;
         if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {

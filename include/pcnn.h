@@ -74,6 +74,10 @@ int pcnn_version(void);
 /* Number of visible CUDA devices (0 if none); never fails. */
 int pcnn_device_count(void);
 
+/* Scratch memory (query ordering, scans) comes from a library-owned stream-ordered pool that
+ * keeps freed blocks for reuse; this returns the cached blocks of `device` to the driver. */
+int pcnn_release_cached(int device);
+
 /* ------------------------------------------------------------------ index build
  * Replaces KDTreeConstruction(db, leaf_size) (kdtree.hpp:419-429) and
  * OctreeConstruction(db, leaf_size, min_extent) (octree.hpp:242-271).
@@ -120,7 +124,8 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
 /* Query-side knobs (all have working defaults).  `sort_queries`: 1 = order queries along
  * the Morton curve before the search (default), 0 = caller's order, e.g. already coherent.
  * `method`: 0 = auto, 1 = thread-per-query traversal, 2 = warp-per-query traversal,
- * 3 = brute-force tiles.  Returns PCNN_ERR_INVALID for unknown values. */
+ * 3 = brute-force tiles, 4 = warp-coherent traversal (32 neighbouring queries share one
+ * walk).  Returns PCNN_ERR_INVALID for unknown values. */
 int pcnn_set_option(pcnn_index* index, const char* name, int value);
 /* With option "profile" = 1 every pcnn_knn / pcnn_radius_* call on this handle brackets its
  * main search kernel (not the query ordering) with CUDA events on the call's stream;

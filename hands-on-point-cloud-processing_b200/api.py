@@ -58,7 +58,7 @@ EXPORTS = [
     "pcnn_knn_host", "pcnn_set_option", "pcnn_get_profile", "pcnn_radius_count", "pcnn_radius_fill",
     "pcnn_radius_host", "pcnn_icp", "pcnn_icp_host", "pcnn_icp_create", "pcnn_icp_accumulate",
     "pcnn_icp_sums_dev", "pcnn_icp_update", "pcnn_icp_finish", "pcnn_icp_destroy", "pcnn_nn1_f32",
-    "pcnn_release_cached",
+    "pcnn_release_cached", "pcnn_debug_warp_times",
 ]
 
 
@@ -98,6 +98,7 @@ def lib():
     L.pcnn_icp_destroy.argtypes = [vp]
     L.pcnn_nn1_f32.argtypes = [vp, vp, i64, i32, vp, vp, vp]
     L.pcnn_release_cached.argtypes = [i32]
+    L.pcnn_debug_warp_times.argtypes = [vp, vp]
     for name in EXPORTS:
         f = getattr(L, name)
         if name not in ("pcnn_last_error", "pcnn_icp_sums_dev"):

@@ -361,6 +361,12 @@ int pcnn_index_get_info(const pcnn_index* index, pcnn_index_info* out) {
     return PCNN_OK;
 }
 
+int pcnn_debug_warp_times(pcnn_index* index, unsigned long long* buf_dev) {
+    PCNN_CHECK_ARG(index != nullptr, "pcnn_debug_warp_times: index is NULL");
+    index->dbg_warp_times = buf_dev;
+    return PCNN_OK;
+}
+
 int pcnn_release_cached(int device) {
     DeviceGuard g(device);
     if (!g.ok) { set_error("pcnn_release_cached: cannot select CUDA device %d", device); return PCNN_ERR_CUDA; }
@@ -387,7 +393,7 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: sort_queries must be 0 or 1");
         index->opt_sort_queries = value;
     } else if (!std::strcmp(name, "method")) {
-        PCNN_CHECK_ARG(value >= 0 && value <= 4, "pcnn_set_option: method must be 0..4");
+        PCNN_CHECK_ARG(value >= 0 && value <= 7, "pcnn_set_option: method must be 0..7");
         index->opt_method = value;
     } else if (!std::strcmp(name, "profile")) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: profile must be 0 or 1");
@@ -403,6 +409,12 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
     } else if (!std::strcmp(name, "coherent_leaf_log")) {
         PCNN_CHECK_ARG(value >= 0 && value <= 6, "pcnn_set_option: coherent_leaf_log must be 0..6");
         index->opt_coherent_leaf_log = value;
+    } else if (!std::strcmp(name, "coherent_budget")) {
+        PCNN_CHECK_ARG(value >= 0, "pcnn_set_option: coherent_budget must be >= 0");
+        index->opt_coherent_budget = value;
+    } else if (!std::strcmp(name, "coherent_budget2")) {
+        PCNN_CHECK_ARG(value >= 0, "pcnn_set_option: coherent_budget2 must be >= 0");
+        index->opt_coherent_budget2 = value;
     } else {
         set_error("pcnn_set_option: unknown option '%s'", name);
         return PCNN_ERR_INVALID;

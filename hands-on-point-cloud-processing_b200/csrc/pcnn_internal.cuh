@@ -27,7 +27,10 @@ struct pcnn_index {
     int opt_method = 0;
     int opt_leaf_log = 1;       // thread-per-query leaf = 2^leaf_log groups
     int opt_warp_leaf_log = 2;  // warp-per-query leaf = 32 points
-    int opt_coherent_leaf_log = 0;  // warp-coherent traversal: leaf = 2^this groups
+    int opt_coherent_leaf_log = 1;  // warp-coherent traversal: leaf = 2^this groups
+    int opt_coherent_budget = 150;   // box tests + group scans a warp may spend before it re-seeds; 0 = never
+    int opt_coherent_budget2 = 600;  // ... and after the re-seed before it hands its queries over; 0 = never
+    unsigned long long* dbg_warp_times = nullptr;  // diagnostics (pcnn_debug_warp_times)
     int opt_profile = 0;
     cudaEvent_t prof0 = nullptr, prof1 = nullptr;  // bracket the last main search kernel
     // staging state of the host-pointer entry points (streams + device buffers), created on

@@ -116,7 +116,7 @@ __device__ __forceinline__ void scan_group_shared(const IndexView& iv, int g, bo
             const int id = __float_as_int(p.w);
             if (d <= tk.worst() && tk.accepts(d, id)) {
                 tk.insert(d, id);
-                wf = ru32(tk.worst());
+                wf = fminf(wf, ru32(tk.worst()));  // wf may already be tighter (box upper bounds)
             }
         }
     }
@@ -126,9 +126,17 @@ template <int K>
 __global__ void __launch_bounds__(KT_THREADS)
 knn_coherent_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                     const unsigned* __restrict__ perm, int k, int leaf_log, int32_t* __restrict__ out_idx,
-                    float* __restrict__ out_dist, double* __restrict__ out_dist64) {
+                    float* __restrict__ out_dist, double* __restrict__ out_dist64, int budget,
+                    int budget2, int* __restrict__ qlist, int* __restrict__ qcount,
+                    unsigned long long* __restrict__ dbg) {
     const unsigned full = 0xffffffffu;
     const int t = blockIdx.x * KT_THREADS + threadIdx.x;
+    bool handed_over = false;
+    unsigned long long dbg_t0 = 0, dbg_c0 = 0;
+    if (dbg) {  // diagnostics: per-warp start time (ns) and duration (cycles)
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+        dbg_c0 = clock64();
+    }
     const bool live = t < nq;
     const int tt = live ? t : nq - 1;  // tail lanes shadow the last query so the warp stays whole
     const int qi = perm ? (int)perm[tt] : tt;
@@ -166,7 +174,71 @@ knn_coherent_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
         g_hi = __reduce_max_sync(full, g_hi);
         int i = g_lo;
         int l = i == 0 ? top : min(__ffs(i) - 1, top);
+        int steps = 0;  // box tests + group scans of this warp (uniform)
+        bool reseeded = false;
         while (i <= g_hi) {
+            if (steps > budget) {
+                if (!reseeded) {
+                    // The sweep drags on: some lane's seed bound is poor (its Morton neighbours are
+                    // not its spatial neighbours, e.g. a query next to a coarse cell boundary of
+                    // the curve).  Tighten the bounds WITHOUT scanning points: walk the rest of
+                    // the window once on boxes only; a full leaf box holds >= K points, all of
+                    // them within its farthest corner, so that distance bounds the k-th neighbour.
+                    reseeded = true;
+                    steps = 0;
+                    budget = budget2;
+                    constexpr int LD = K <= 8 ? 0 : 1;  // 8 << LD points per leaf box >= K
+                    int i2 = i, l2 = l;
+                    while (i2 <= g_hi) {
+                        const int node = i2 >> l2;
+                        const float4* bb = iv.box + 2 * ((size_t)iv.lev_off[l2] + node);
+                        const float4 lo = __ldg(bb), hi = __ldg(bb + 1);
+                        const float lbf = lbsq32(boxgap_rd(lo.x, hi.x, qxf), boxgap_rd(lo.y, hi.y, qyf),
+                                                 boxgap_rd(lo.z, hi.z, qzf));
+                        const bool need = !(lbf > wf);
+                        if (!__any_sync(full, need)) {
+                            i2 = (node + 1) << l2;
+                            if (i2 >= iv.n0) break;
+                            l2 = min(__ffs(i2) - 1, top);
+                            continue;
+                        }
+                        if (l2 > LD) {
+                            l2 -= 1;
+                            continue;
+                        }
+                        if (((long long)(node + 1) << (l2 + PCNN_GROUP_LOG)) <= (long long)iv.n) {
+                            // farthest corner, rounded up, with the same 2^-20 margin as the lower bound
+                            const float ax = fmaxf(fabsf(__fsub_ru(qxf, lo.x)), fabsf(__fsub_ru(hi.x, qxf)));
+                            const float ay = fmaxf(fabsf(__fsub_ru(qyf, lo.y)), fabsf(__fsub_ru(hi.y, qyf)));
+                            const float az = fmaxf(fabsf(__fsub_ru(qzf, lo.z)), fabsf(__fsub_ru(hi.z, qzf)));
+                            const float ub = __fmul_ru(
+                                __fadd_ru(__fadd_ru(__fmul_ru(ax, ax), __fmul_ru(ay, ay)), __fmul_ru(az, az)),
+                                1.000001f);
+                            wf = fminf(wf, ub);
+                        }
+                        i2 = (node + 1) << l2;
+                        if (i2 >= iv.n0) break;
+                        l2 = min(__ffs(i2) - 1, top);
+                    }
+                    int nh = iv.n0 - 1;
+                    if (wf < 3.0e38f) {
+                        const float r = __fmul_ru(__fsqrt_ru(wf), 1.000001f);
+                        const float hx = __fadd_ru(qxf, r), hy = __fadd_ru(qyf, r), hz = __fadd_ru(qzf, r);
+                        nh = home_group(iv, morton63(hx, hy, hz, iv.cube, iv.cube[3]));
+                    }
+                    g_hi = __reduce_max_sync(full, nh);
+                    continue;
+                }
+                // still dragging on: hand the warp's queries to the nearest-first kernel
+                const unsigned m = __ballot_sync(full, live);
+                int base = 0;
+                if ((threadIdx.x & 31) == 0) base = atomicAdd(qcount, __popc(m));
+                base = __shfl_sync(full, base, 0);
+                if (live) qlist[base + __popc(m & ((1u << (threadIdx.x & 31)) - 1u))] = qi;
+                handed_over = true;
+                break;
+            }
+            steps++;
             const int node = i >> l;
             const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + node);
             const float4 lo = __ldg(b), hi = __ldg(b + 1);
@@ -187,14 +259,514 @@ knn_coherent_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
             if (g1 > iv.n0) g1 = iv.n0;
             for (int g = g0; g < g1; g++) {
                 const bool mine = need && (g < h0 || g > h1);
-                if (__any_sync(full, mine)) scan_group_shared<K>(iv, g, mine, qxf, qyf, qzf, qx, qy, qz, tk, wf);
+                if (__any_sync(full, mine)) {
+                    scan_group_shared<K>(iv, g, mine, qxf, qyf, qzf, qx, qy, qz, tk, wf);
+                    steps++;
+                }
             }
             i = g1;
             if (i >= iv.n0) break;
             l = min(__ffs(i) - 1, top);
         }
     }
+    if (live && !handed_over) write_row<K>(tk, qi, k, out_idx, out_dist, out_dist64);
+    if (dbg && (threadIdx.x & 31) == 0) {
+        dbg[2 * (size_t)(t >> 5)] = dbg_t0;
+        dbg[2 * (size_t)(t >> 5) + 1] = (unsigned long long)(clock64() - dbg_c0);
+    }
+}
+
+// ------------------------------------------------------------------ shared walk, per-lane scan queues
+// Same shared, warp-uniform walk over the boxes as knn_coherent_kernel, but a lane that needs a
+// group does not make the whole warp scan it: it pushes the group on its own small queue (shared
+// memory).  When some lane's queue is full all lanes drain their queues together, every lane
+// scanning ITS OWN next group in lock step -- in a coherent warp those are the same addresses
+// (broadcast loads), in a warp that straddles a jump of the curve the lanes work on different
+// places at the same time.  The warp then pays for the largest per-lane need, not for the sum.
+constexpr int KQ_DEPTH = 8;  // queue entries per lane
+
+template <int K>
+__device__ __forceinline__ void scan_own_group(const IndexView& iv, int g, bool active, float qxf, float qyf,
+                                               float qzf, double qx, double qy, double qz, TopK<K>& tk,
+                                               float& wf, int& ins_rounds) {
+    const unsigned full = 0xffffffffu;
+    const int first = g << PCNN_GROUP_LOG;
+    unsigned pass = 0;
+    if (active) {
+        const int cnt = (iv.n - first) < PCNN_GROUP ? (iv.n - first) : PCNN_GROUP;
+#pragma unroll
+        for (int j = 0; j < PCNN_GROUP; j++) {
+            if (j < cnt) {
+                const float4 p = __ldg(iv.pts + first + j);
+                const float lbf = lbsq32(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
+                if (!(lbf > wf)) pass |= 1u << j;
+            }
+        }
+    }
+    while (__any_sync(full, pass != 0)) {
+        ins_rounds++;
+        if (pass) {
+            const int j = __ffs((int)pass) - 1;
+            pass &= pass - 1;
+            const float4 p = __ldg(iv.pts + first + j);
+            const double d = key64(p.x, p.y, p.z, qx, qy, qz);
+            const int id = __float_as_int(p.w);
+            if (d <= tk.worst() && tk.accepts(d, id)) {
+                tk.insert(d, id);
+                wf = fminf(wf, ru32(tk.worst()));
+            }
+        }
+    }
+}
+
+template <int K>
+__global__ void __launch_bounds__(KT_THREADS)
+knn_queue_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
+                 const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
+                 float* __restrict__ out_dist, double* __restrict__ out_dist64, int budget,
+                 unsigned long long* __restrict__ dbg) {
+    __shared__ int s_qg[KQ_DEPTH][KT_THREADS];
+    __shared__ float s_ql[KQ_DEPTH][KT_THREADS];
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x;
+    const int t = blockIdx.x * KT_THREADS + tid;
+    unsigned long long dbg_t0 = 0, dbg_c0 = 0;
+    if (dbg) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+        dbg_c0 = clock64();
+    }
+    const bool live = t < nq;
+    const int tt = live ? t : nq - 1;
+    const int qi = perm ? (int)perm[tt] : tt;
+    const float* qp = q + (size_t)qi * stride;
+    const float qxf = qp[0], qyf = qp[1], qzf = qp[2];
+    const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
+    TopK<K> tk;
+    tk.init();
+    int c_box = 0, c_scan = 0, c_ins = 0, c_rbox = 0, c_drain = 0, g_lo_dbg = 0, g_hi_dbg = 0;  // diagnostics
+    if (iv.n > 0) {
+        float wf = __int_as_float(0x7f800000);
+        int cnt = 0;  // entries on this lane's queue
+        int steps = 0;
+#define KQ_DRAIN()                                                                                   \
+        do {                                                                                         \
+            const int maxc = __reduce_max_sync(full, cnt);                                           \
+            c_drain++;                                                                               \
+            for (int r = 0; r < maxc; r++) {                                                         \
+                const bool act = r < cnt && !(s_ql[r][tid] > wf);                                    \
+                if (__any_sync(full, act)) {                                                         \
+                    scan_own_group<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins); \
+                    steps++;                                                                         \
+                    c_scan++;                                                                        \
+                }                                                                                    \
+            }                                                                                        \
+            cnt = 0;                                                                                 \
+        } while (0)
+
+        // seed: own home group and its two neighbours
+        const int h = home_group(iv, morton63(qxf, qyf, qzf, iv.cube, iv.cube[3]));
+        const int h0 = h > 0 ? h - 1 : 0, h1 = (h + 1 < iv.n0) ? h + 1 : iv.n0 - 1;
+        for (int g = h0; g <= h1; g++) { s_qg[cnt][tid] = g; s_ql[cnt][tid] = 0.f; cnt++; }
+        KQ_DRAIN();
+        const int top = iv.nlev - 1;
+        int g_lo = 0, g_hi = iv.n0 - 1;
+        if (wf < 3.0e38f) {
+            const float r = __fmul_ru(__fsqrt_ru(wf), 1.000001f);
+            const float lx = __fsub_rd(qxf, r), ly = __fsub_rd(qyf, r), lz = __fsub_rd(qzf, r);
+            const float hx = __fadd_ru(qxf, r), hy = __fadd_ru(qyf, r), hz = __fadd_ru(qzf, r);
+            g_lo = group_before(iv, morton63(lx, ly, lz, iv.cube, iv.cube[3]));
+            g_hi = home_group(iv, morton63(hx, hy, hz, iv.cube, iv.cube[3]));
+        }
+        g_lo = __reduce_min_sync(full, g_lo);
+        g_hi = __reduce_max_sync(full, g_hi);
+        g_lo_dbg = g_lo; g_hi_dbg = g_hi;
+        int i = g_lo;
+        int l = i == 0 ? top : min(__ffs(i) - 1, top);
+        bool reseeded = false;
+        steps = 0;
+        while (i <= g_hi) {
+            if (steps > budget && !reseeded) {
+                // Poor seed somewhere in the warp: tighten the bounds on boxes alone over the rest
+                // of the window (a full group box holds 8 >= K points... or 16 at level 1, all
+                // within its farthest corner), then go on.
+                reseeded = true;
+                KQ_DRAIN();
+                constexpr int LD = K <= 8 ? 0 : 1;
+                int i2 = i, l2 = l;
+                while (i2 <= g_hi) {
+                    c_rbox++;
+                    const int node = i2 >> l2;
+                    const float4* bb = iv.box + 2 * ((size_t)iv.lev_off[l2] + node);
+                    const float4 lo = __ldg(bb), hi = __ldg(bb + 1);
+                    const float lbf = lbsq32(boxgap_rd(lo.x, hi.x, qxf), boxgap_rd(lo.y, hi.y, qyf),
+                                             boxgap_rd(lo.z, hi.z, qzf));
+                    const bool need = !(lbf > wf);
+                    if (!__any_sync(full, need)) {
+                        i2 = (node + 1) << l2;
+                        if (i2 >= iv.n0) break;
+                        l2 = min(__ffs(i2) - 1, top);
+                        continue;
+                    }
+                    if (l2 > LD) {
+                        l2 -= 1;
+                        continue;
+                    }
+                    if (((long long)(node + 1) << (l2 + PCNN_GROUP_LOG)) <= (long long)iv.n) {
+                        const float ax = fmaxf(fabsf(__fsub_ru(qxf, lo.x)), fabsf(__fsub_ru(hi.x, qxf)));
+                        const float ay = fmaxf(fabsf(__fsub_ru(qyf, lo.y)), fabsf(__fsub_ru(hi.y, qyf)));
+                        const float az = fmaxf(fabsf(__fsub_ru(qzf, lo.z)), fabsf(__fsub_ru(hi.z, qzf)));
+                        const float ub = __fmul_ru(
+                            __fadd_ru(__fadd_ru(__fmul_ru(ax, ax), __fmul_ru(ay, ay)), __fmul_ru(az, az)),
+                            1.000001f);
+                        wf = fminf(wf, ub);
+                    }
+                    i2 = (node + 1) << l2;
+                    if (i2 >= iv.n0) break;
+                    l2 = min(__ffs(i2) - 1, top);
+                }
+                int nh = iv.n0 - 1;
+                if (wf < 3.0e38f) {
+                    const float r = __fmul_ru(__fsqrt_ru(wf), 1.000001f);
+                    const float hx = __fadd_ru(qxf, r), hy = __fadd_ru(qyf, r), hz = __fadd_ru(qzf, r);
+                    nh = home_group(iv, morton63(hx, hy, hz, iv.cube, iv.cube[3]));
+                }
+                g_hi = __reduce_max_sync(full, nh);
+                continue;
+            }
+            steps++;
+            c_box++;
+            const int node = i >> l;
+            const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + node);
+            const float4 lo = __ldg(b), hi = __ldg(b + 1);
+            const float lbf = lbsq32(boxgap_rd(lo.x, hi.x, qxf), boxgap_rd(lo.y, hi.y, qyf),
+                                     boxgap_rd(lo.z, hi.z, qzf));
+            const bool need = !(lbf > wf);
+            if (!__any_sync(full, need)) {
+                i = (node + 1) << l;
+                if (i >= iv.n0) break;
+                l = min(__ffs(i) - 1, top);
+                continue;
+            }
+            if (l > 0) {
+                l -= 1;
+                continue;
+            }
+            if (need && (node < h0 || node > h1)) {
+                s_qg[cnt][tid] = node;
+                s_ql[cnt][tid] = lbf;
+                cnt++;
+            }
+            if (__any_sync(full, cnt >= KQ_DEPTH)) KQ_DRAIN();
+            i = node + 1;
+            if (i >= iv.n0) break;
+            l = min(__ffs(i) - 1, top);
+        }
+        KQ_DRAIN();
+#undef KQ_DRAIN
+    }
     if (live) write_row<K>(tk, qi, k, out_idx, out_dist, out_dist64);
+    if (dbg && (tid & 31) == 0) {
+        dbg[2 * (size_t)(t >> 5)] = dbg_t0;
+        dbg[2 * (size_t)(t >> 5) + 1] = (unsigned long long)(clock64() - dbg_c0);
+        unsigned long long* c = dbg + 2 * (size_t)((nq + 31) / 32) + 8 * (size_t)(t >> 5);
+        c[0] = c_box; c[1] = c_scan; c[2] = c_ins; c[3] = c_rbox; c[4] = c_drain;
+        c[5] = (unsigned long long)(g_hi_dbg - g_lo_dbg);
+    }
+}
+
+// ------------------------------------------------------------------ lock-step per-lane walks
+// Every lane walks the hierarchy for its OWN query (own position, own window, own bound), but
+// the warp executes the walks in lock step: a round is a fixed sequence of predicated box
+// steps (no data-dependent inner loops for the hardware to serialise), groups a lane needs go
+// to its queue, and queues are drained together with synchronised exact-insert rounds.  A warp
+// costs the LONGEST lane walk, and its 32 box loads per step are in flight at once -- against
+// the shared walk above, whose cost is the UNION of the lanes' walks, one dependent load at a
+// time.  A lane whose walk drags on (poor Morton seed) switches to a boxes-only pass over the
+// rest of its window that tightens its bound from the far corners of full leaf boxes, then
+// resumes.
+constexpr int KL_WALK = 8;  // box steps per round
+
+template <int K>
+__global__ void __launch_bounds__(KT_THREADS)
+knn_lockstep_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
+                    const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
+                    float* __restrict__ out_dist, double* __restrict__ out_dist64, int budget,
+                    unsigned long long* __restrict__ dbg) {
+    __shared__ int s_qg[KQ_DEPTH][KT_THREADS];
+    __shared__ float s_ql[KQ_DEPTH][KT_THREADS];
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x;
+    const int t = blockIdx.x * KT_THREADS + tid;
+    unsigned long long dbg_t0 = 0, dbg_c0 = 0;
+    if (dbg) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+        dbg_c0 = clock64();
+    }
+    const bool live = t < nq;
+    const int tt = live ? t : nq - 1;
+    const int qi = perm ? (int)perm[tt] : tt;
+    const float* qp = q + (size_t)qi * stride;
+    const float qxf = qp[0], qyf = qp[1], qzf = qp[2];
+    const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
+    TopK<K> tk;
+    tk.init();
+    int c_round = 0, c_scan = 0, c_ins = 0, c_steps = 0, c_tight = 0;  // diagnostics
+    if (iv.n > 0) {
+        float wf = __int_as_float(0x7f800000);
+        int cnt = 0;
+#define KL_DRAIN()                                                                                   \
+        do {                                                                                         \
+            const int maxc = __reduce_max_sync(full, cnt);                                           \
+            for (int r = 0; r < maxc; r++) {                                                         \
+                const bool act = r < cnt && !(s_ql[r][tid] > wf);                                    \
+                if (__any_sync(full, act)) {                                                         \
+                    scan_own_group<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins); \
+                    c_scan++;                                                                        \
+                }                                                                                    \
+            }                                                                                        \
+            cnt = 0;                                                                                 \
+        } while (0)
+
+        const int h = home_group(iv, morton63(qxf, qyf, qzf, iv.cube, iv.cube[3]));
+        const int h0 = h > 0 ? h - 1 : 0, h1 = (h + 1 < iv.n0) ? h + 1 : iv.n0 - 1;
+        for (int g = h0; g <= h1; g++) { s_qg[cnt][tid] = g; s_ql[cnt][tid] = 0.f; cnt++; }
+        KL_DRAIN();
+        const int top = iv.nlev - 1;
+        int g_lo = 0, g_hi = iv.n0 - 1;
+        if (wf < 3.0e38f) {
+            const float r = __fmul_ru(__fsqrt_ru(wf), 1.000001f);
+            const float lx = __fsub_rd(qxf, r), ly = __fsub_rd(qyf, r), lz = __fsub_rd(qzf, r);
+            const float hx = __fadd_ru(qxf, r), hy = __fadd_ru(qyf, r), hz = __fadd_ru(qzf, r);
+            g_lo = group_before(iv, morton63(lx, ly, lz, iv.cube, iv.cube[3]));
+            g_hi = home_group(iv, morton63(hx, hy, hz, iv.cube, iv.cube[3]));
+        }
+        // walk state of this lane
+        int i = g_lo;
+        int l = i == 0 ? top : min(__ffs(i) - 1, top);
+        bool done = i > g_hi;
+        int mode = 0;          // 0 = collect groups, 1 = boxes-only bound tightening
+        int si = 0, sl = 0;    // saved position while in mode 1
+        int mysteps = 0;
+        bool tightened = false;
+        constexpr int LD = K <= 8 ? 0 : 1;  // 8 << LD points per box >= K
+        while (true) {
+            c_round++;
+#pragma unroll 1
+            for (int s = 0; s < KL_WALK; s++) {
+                const bool can = !done && cnt < KQ_DEPTH;
+                if (!__any_sync(full, can)) break;
+                if (can) {
+                    mysteps++;
+                    const int node = i >> l;
+                    const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + node);
+                    const float4 lo = __ldg(b), hi = __ldg(b + 1);
+                    const float lbf = lbsq32(boxgap_rd(lo.x, hi.x, qxf), boxgap_rd(lo.y, hi.y, qyf),
+                                             boxgap_rd(lo.z, hi.z, qzf));
+                    const bool need = !(lbf > wf);
+                    const int floor_l = mode ? LD : 0;
+                    if (need && l > floor_l) {
+                        l -= 1;
+                    } else {
+                        if (need) {
+                            if (mode == 0) {
+                                if (node < h0 || node > h1) {
+                                    s_qg[cnt][tid] = node;
+                                    s_ql[cnt][tid] = lbf;
+                                    cnt++;
+                                }
+                            } else if (((long long)(node + 1) << (l + PCNN_GROUP_LOG)) <= (long long)iv.n) {
+                                const float ax = fmaxf(fabsf(__fsub_ru(qxf, lo.x)), fabsf(__fsub_ru(hi.x, qxf)));
+                                const float ay = fmaxf(fabsf(__fsub_ru(qyf, lo.y)), fabsf(__fsub_ru(hi.y, qyf)));
+                                const float az = fmaxf(fabsf(__fsub_ru(qzf, lo.z)), fabsf(__fsub_ru(hi.z, qzf)));
+                                const float ub = __fmul_ru(
+                                    __fadd_ru(__fadd_ru(__fmul_ru(ax, ax), __fmul_ru(ay, ay)), __fmul_ru(az, az)),
+                                    1.000001f);
+                                wf = fminf(wf, ub);
+                            }
+                        }
+                        i = (node + 1) << l;
+                        l = min(__ffs(i) - 1, top);
+                        if (i > g_hi || i >= iv.n0) {
+                            if (mode == 1) {  // tightening pass finished: resume collecting
+                                mode = 0;
+                                i = si;
+                                l = sl;
+                            } else {
+                                done = true;
+                            }
+                        }
+                    }
+                    if (mode == 0 && !tightened && !done && mysteps > budget) {
+                        tightened = true;
+                        c_tight++;
+                        mode = 1;
+                        si = i;
+                        sl = l;
+                    }
+                }
+            }
+            KL_DRAIN();
+            if (!__any_sync(full, !done)) break;
+        }
+#undef KL_DRAIN
+        c_steps = mysteps;
+    }
+    if (live) write_row<K>(tk, qi, k, out_idx, out_dist, out_dist64);
+    if (dbg) {
+        const int maxsteps = __reduce_max_sync(full, c_steps);
+        const int sumsteps = __reduce_add_sync(full, c_steps);
+        const int ntight = __reduce_add_sync(full, c_tight);
+        if ((tid & 31) == 0) {
+            dbg[2 * (size_t)(t >> 5)] = dbg_t0;
+            dbg[2 * (size_t)(t >> 5) + 1] = (unsigned long long)(clock64() - dbg_c0);
+            unsigned long long* c = dbg + 2 * (size_t)((nq + 31) / 32) + 8 * (size_t)(t >> 5);
+            c[0] = maxsteps; c[1] = c_scan; c[2] = c_ins; c[3] = sumsteps; c[4] = c_round; c[5] = ntight;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ lock-step nearest-first walks
+// The order of the reference's own search (near child first, kdtree.hpp:347-363), without its
+// recursion: every lane runs a depth-first walk of the binary hierarchy for its own query,
+// examining the two children of a node per step (one 64-byte fetch), descending into the
+// nearer one and remembering in ONE 32-bit mask at which levels the farther sibling is still
+// owed a visit -- the tree is complete, so that sibling is index arithmetic on the current
+// node, no stack.  Nearest-first means the first leaf reached already gives a bound close to
+// the final one wherever the query sits, including next to a coarse cell boundary of the
+// curve where the Morton neighbours are not the spatial ones.  The warp runs the 32 walks in
+// lock step (fixed rounds of predicated steps), groups a lane needs go to its queue and the
+// queues are drained together, as in knn_lockstep_kernel.
+template <int K>
+__global__ void __launch_bounds__(KT_THREADS)
+knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
+               const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
+               float* __restrict__ out_dist, double* __restrict__ out_dist64,
+               unsigned long long* __restrict__ dbg) {
+    __shared__ int s_qg[KQ_DEPTH][KT_THREADS];
+    __shared__ float s_ql[KQ_DEPTH][KT_THREADS];
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x;
+    const int t = blockIdx.x * KT_THREADS + tid;
+    unsigned long long dbg_t0 = 0, dbg_c0 = 0;
+    if (dbg) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+        dbg_c0 = clock64();
+    }
+    const bool live = t < nq;
+    const int tt = live ? t : nq - 1;
+    const int qi = perm ? (int)perm[tt] : tt;
+    const float* qp = q + (size_t)qi * stride;
+    const float qxf = qp[0], qyf = qp[1], qzf = qp[2];
+    const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
+    TopK<K> tk;
+    tk.init();
+    int c_round = 0, c_scan = 0, c_ins = 0, c_steps = 0;  // diagnostics
+    if (iv.n > 0) {
+        const float INFf = __int_as_float(0x7f800000);
+        float wf = INFf;
+        int cnt = 0;
+        const int top = iv.nlev - 1;
+        const unsigned long long qcode = morton63(qxf, qyf, qzf, iv.cube, iv.cube[3]);
+        int l = top, n = 0;      // current node
+        unsigned pending = 0;    // bit L: the sibling of our ancestor at level L is still to visit
+        int mode = 0;            // 0 = examine the children of (l, n); 1 = backtrack
+        bool done = false;
+        // seed: the group holding the query's Morton code and its two neighbours give a first
+        // bound, so the walk prunes from its first step
+        const int h = home_group(iv, qcode);
+        const int h0 = h > 0 ? h - 1 : 0, h1 = (h + 1 < iv.n0) ? h + 1 : iv.n0 - 1;
+        for (int g = h0; g <= h1; g++) { s_qg[cnt][tid] = g; s_ql[cnt][tid] = 0.f; cnt++; }
+        if (top == 0) done = true;  // a single group, already queued
+        while (true) {
+            c_round++;
+#pragma unroll 1
+            for (int s = 0; s < KL_WALK; s++) {
+                // a lane waits for a drain when its queue may overflow or it has no bound yet
+                const bool can = !done && cnt <= KQ_DEPTH - 2 && !(cnt > 0 && wf > 3.0e38f);
+                if (!__any_sync(full, can)) break;
+                if (can) {
+                    int L, P, far = 0;
+                    if (mode == 0) {
+                        L = l - 1;
+                        P = 2 * n;
+                    } else if (pending == 0) {
+                        done = true;
+                        L = 0;
+                        P = 0;
+                    } else {
+                        const int lp = __ffs((int)pending) - 1;
+                        pending &= pending - 1;
+                        far = (n >> (lp - l)) ^ 1;
+                        l = lp;
+                        n = far;
+                        L = lp;
+                        P = far & ~1;
+                    }
+                    if (!done) {
+                        c_steps++;
+                        const int cl = (int)(((long long)iv.n0 + (1LL << L) - 1) >> L);
+                        const float4* b = iv.box + 2 * ((size_t)iv.lev_off[L] + P);
+                        const float4 alo = __ldg(b), ahi = __ldg(b + 1);
+                        const float lbA = lbsq32(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
+                                                 boxgap_rd(alo.z, ahi.z, qzf));
+                        float lbB = INFf;
+                        const bool hasB = P + 1 < cl;
+                        if (hasB) {
+                            const float4 blo = __ldg(b + 2), bhi = __ldg(b + 3);
+                            lbB = lbsq32(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
+                                         boxgap_rd(blo.z, bhi.z, qzf));
+                        }
+                        if (mode == 0) {
+                            bool first1 = lbB < lbA;
+                            if (hasB && lbB == lbA)  // tie (query inside both boxes): follow the curve
+                                first1 = qcode >= __ldg(iv.gcode + ((size_t)(P + 1) << L));
+                            const float lbn = first1 ? lbB : lbA, lbf2 = first1 ? lbA : lbB;
+                            const int near = P + (first1 ? 1 : 0);
+                            const bool passN = !(lbn > wf);
+                            const bool passF = !(lbf2 > wf) && lbf2 < INFf;
+                            if (L == 0) {
+                                if (passN && (near < h0 || near > h1)) { s_qg[cnt][tid] = near; s_ql[cnt][tid] = lbn; cnt++; }
+                                if (passF && ((near ^ 1) < h0 || (near ^ 1) > h1)) { s_qg[cnt][tid] = near ^ 1; s_ql[cnt][tid] = lbf2; cnt++; }
+                                mode = 1;
+                            } else if (passN) {
+                                if (passF) pending |= 1u << L;
+                                l = L;
+                                n = near;
+                            } else {
+                                mode = 1;
+                            }
+                        } else {
+                            const float lbv = (far & 1) ? lbB : lbA;
+                            if (!(lbv > wf)) mode = 0;  // visit it: next step examines its children
+                        }
+                    }
+                }
+            }
+            {
+                const int maxc = __reduce_max_sync(full, cnt);
+                for (int r = 0; r < maxc; r++) {
+                    const bool act = r < cnt && !(s_ql[r][tid] > wf);
+                    if (__any_sync(full, act)) {
+                        scan_own_group<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
+                        c_scan++;
+                    }
+                }
+                cnt = 0;
+            }
+            if (!__any_sync(full, !done)) break;
+        }
+    }
+    if (live) write_row<K>(tk, qi, k, out_idx, out_dist, out_dist64);
+    if (dbg) {
+        const int maxsteps = __reduce_max_sync(full, c_steps);
+        const int sumsteps = __reduce_add_sync(full, c_steps);
+        if ((tid & 31) == 0) {
+            dbg[2 * (size_t)(t >> 5)] = dbg_t0;
+            dbg[2 * (size_t)(t >> 5) + 1] = (unsigned long long)(clock64() - dbg_c0);
+            unsigned long long* c = dbg + 2 * (size_t)((nq + 31) / 32) + 8 * (size_t)(t >> 5);
+            c[0] = maxsteps; c[1] = c_scan; c[2] = c_ins; c[3] = sumsteps; c[4] = c_round; c[5] = 0;
+        }
+    }
 }
 
 // ------------------------------------------------------------------ brute-force tiles (TMA)
@@ -286,17 +858,13 @@ knn_brute_kernel(const float4* __restrict__ pts, int n, const float* __restrict_
 // running top-k is a 32-entry sorted list, one entry per lane; a candidate is inserted by
 // one ballot (its rank) and one shuffle-up (the shift).  (lo_key, lo_idx) is an exclusive
 // lower bound used to fetch neighbours 33..64, 65..96, ... in further passes.
-__global__ void __launch_bounds__(WQ_WARPS * 32)
-knn_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, int stride,
-                int k_total, int col0, int kk, double* __restrict__ lower_key,
-                int* __restrict__ lower_idx, int32_t* __restrict__ out_idx,
-                float* __restrict__ out_dist, double* __restrict__ out_dist64) {
-    __shared__ float s_lb[WQ_WARPS][WQ_MAXD][32];
-    __shared__ int s_base[WQ_WARPS][WQ_MAXD];
+__device__ __forceinline__ void knn_warp_one(const IndexView& iv, const WarpPlan& wp, float (*s_lb)[32],
+                                             int* s_base, const float* __restrict__ q, int qi, int stride,
+                                             int k_total, int col0, int kk, double* __restrict__ lower_key,
+                                             int* __restrict__ lower_idx, int32_t* __restrict__ out_idx,
+                                             float* __restrict__ out_dist, double* __restrict__ out_dist64) {
     const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int qi = blockIdx.x * WQ_WARPS + w;
-    if (qi >= nq) return;  // warp-uniform
+    const int lane = threadIdx.x & 31;
     const float* qp = q + (size_t)qi * stride;
     const double qx = (double)qp[0], qy = (double)qp[1], qz = (double)qp[2];
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
@@ -319,12 +887,12 @@ knn_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, 
                 const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + lane);
                 lb = boxlb64(__ldg(b), __ldg(b + 1), qx, qy, qz);
             }
-            s_lb[w][0][lane] = (lane < cnt) ? __double2float_rd(lb) : INFf;
-            if (lane == 0) s_base[w][0] = 0;
+            s_lb[0][lane] = (lane < cnt) ? __double2float_rd(lb) : INFf;
+            if (lane == 0) s_base[0] = 0;
             __syncwarp();
         }
         while (true) {
-            const float lbf = s_lb[w][d][lane];
+            const float lbf = s_lb[d][lane];
             const unsigned sel = __reduce_min_sync(full, (__float_as_uint(lbf) & ~31u) | (unsigned)lane);
             const unsigned selb = sel & ~31u;
             if (selb >= 0x7f800000u || (double)__uint_as_float(selb) > wk) {
@@ -333,9 +901,9 @@ knn_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, 
                 continue;
             }
             const int j = (int)(sel & 31u);
-            const int node = s_base[w][d] + j;
+            const int node = s_base[d] + j;
             __syncwarp();
-            if (lane == j) s_lb[w][d][lane] = INFf;  // consumed
+            if (lane == j) s_lb[d][lane] = INFf;  // consumed
             __syncwarp();
             if (d < wp.nd - 1) {
                 const int l = wp.lvl[d + 1];
@@ -349,8 +917,8 @@ knn_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, 
                     lb = boxlb64(__ldg(b), __ldg(b + 1), qx, qy, qz);
                 }
                 d++;
-                s_lb[w][d][lane] = (valid && !(lb > wk)) ? __double2float_rd(lb) : INFf;
-                if (lane == 0) s_base[w][d] = base;
+                s_lb[d][lane] = (valid && !(lb > wk)) ? __double2float_rd(lb) : INFf;
+                if (lane == 0) s_base[d] = base;
                 __syncwarp();
             } else {
                 // leaf: one candidate per lane
@@ -392,6 +960,38 @@ knn_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, 
     if (lower_key && lane == kk - 1) { lower_key[qi] = lk; lower_idx[qi] = li; }
 }
 
+__global__ void __launch_bounds__(WQ_WARPS * 32)
+knn_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, int stride,
+                int k_total, int col0, int kk, double* __restrict__ lower_key,
+                int* __restrict__ lower_idx, int32_t* __restrict__ out_idx,
+                float* __restrict__ out_dist, double* __restrict__ out_dist64) {
+    __shared__ float s_lb[WQ_WARPS][WQ_MAXD][32];
+    __shared__ int s_base[WQ_WARPS][WQ_MAXD];
+    const int w = threadIdx.x >> 5;
+    const int qi = blockIdx.x * WQ_WARPS + w;
+    if (qi >= nq) return;  // warp-uniform
+    knn_warp_one(iv, wp, s_lb[w], s_base[w], q, qi, stride, k_total, col0, kk, lower_key, lower_idx, out_idx,
+                 out_dist, out_dist64);
+}
+
+// Same search for the queries a budgeted kernel gave up on: qlist[0 .. *qcount) holds their
+// ids; a fixed grid of warps walks the list.
+__global__ void __launch_bounds__(WQ_WARPS * 32)
+knn_warp_list_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int stride, int k,
+                     const int* __restrict__ qlist, const int* __restrict__ qcount,
+                     int32_t* __restrict__ out_idx, float* __restrict__ out_dist,
+                     double* __restrict__ out_dist64) {
+    __shared__ float s_lb[WQ_WARPS][WQ_MAXD][32];
+    __shared__ int s_base[WQ_WARPS][WQ_MAXD];
+    const int w = threadIdx.x >> 5;
+    const int total = *qcount;
+    for (int i = blockIdx.x * WQ_WARPS + w; i < total; i += gridDim.x * WQ_WARPS) {
+        knn_warp_one(iv, wp, s_lb[w], s_base[w], q, qlist[i], stride, k, 0, k, nullptr, nullptr, out_idx,
+                     out_dist, out_dist64);
+        __syncwarp();
+    }
+}
+
 // ------------------------------------------------------------------ launcher
 template <int K>
 static void launch_thread_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
@@ -401,9 +1001,32 @@ static void launch_thread_k(const pcnn_index* ix, const float* q, int nq, int st
 }
 template <int K>
 static void launch_coherent_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
-                              int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
+                              int k, int32_t* oi, float* od, double* od64, int* qlist, int* qcount,
+                              cudaStream_t s) {
     knn_coherent_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
-        ix->view, q, nq, stride, perm, k, ix->opt_coherent_leaf_log, oi, od, od64);
+        ix->view, q, nq, stride, perm, k, ix->opt_coherent_leaf_log, oi, od, od64,
+        ix->opt_coherent_budget > 0 ? ix->opt_coherent_budget : 0x7fffffff,
+        qlist ? ix->opt_coherent_budget2 : 0x7fffffff, qlist, qcount, ix->dbg_warp_times);
+}
+template <int K>
+static void launch_queue_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
+                           int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
+    knn_queue_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
+        ix->view, q, nq, stride, perm, k, oi, od, od64,
+        ix->opt_coherent_budget > 0 ? ix->opt_coherent_budget : 0x7fffffff, ix->dbg_warp_times);
+}
+template <int K>
+static void launch_lockstep_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
+                              int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
+    knn_lockstep_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
+        ix->view, q, nq, stride, perm, k, oi, od, od64,
+        ix->opt_coherent_budget > 0 ? ix->opt_coherent_budget : 0x7fffffff, ix->dbg_warp_times);
+}
+template <int K>
+static void launch_dfs_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
+                         int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
+    knn_dfs_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
+        ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
 }
 template <int K>
 static void launch_brute_k(const pcnn_index* ix, const float* q, int nq, int stride, int k, int32_t* oi,
@@ -418,9 +1041,9 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     const int nq = (int)nq64;
     int method = ix->opt_method;
     if (method == 0) method = (k <= 16) ? 4 : 2;
-    if ((method == 1 || method == 3 || method == 4) && k > 16) method = 2;
+    if ((method == 1 || method == 3 || method == 4 || method == 5 || method == 6 || method == 7) && k > 16) method = 2;
     if (method == 3 && ix->n == 0) method = 1;
-    if (method == 4) {
+    if (method == 7) {
         Scratch sc(s);
         unsigned* perm = nullptr;
         if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
@@ -428,11 +1051,67 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
             if (rc != PCNN_OK) return rc;
         }
         prof_begin(ix, s);
-        if (k <= 1) launch_coherent_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
-        else if (k <= 2) launch_coherent_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
-        else if (k <= 4) launch_coherent_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
-        else if (k <= 8) launch_coherent_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
-        else launch_coherent_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        if (k <= 1) launch_dfs_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 2) launch_dfs_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 4) launch_dfs_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 8) launch_dfs_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else launch_dfs_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        prof_end(ix, s);
+    } else if (method == 6) {
+        Scratch sc(s);
+        unsigned* perm = nullptr;
+        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+            int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+            if (rc != PCNN_OK) return rc;
+        }
+        prof_begin(ix, s);
+        if (k <= 1) launch_lockstep_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 2) launch_lockstep_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 4) launch_lockstep_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 8) launch_lockstep_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else launch_lockstep_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        prof_end(ix, s);
+    } else if (method == 5) {
+        Scratch sc(s);
+        unsigned* perm = nullptr;
+        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+            int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+            if (rc != PCNN_OK) return rc;
+        }
+        prof_begin(ix, s);
+        if (k <= 1) launch_queue_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 2) launch_queue_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 4) launch_queue_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 8) launch_queue_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else launch_queue_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        prof_end(ix, s);
+    } else if (method == 4) {
+        Scratch sc(s);
+        unsigned* perm = nullptr;
+        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+            int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+            if (rc != PCNN_OK) return rc;
+        }
+        // queries whose warp exceeds the sweep budget are finished by the nearest-first kernel
+        int *qlist = nullptr, *qcount = nullptr;
+        if (ix->opt_coherent_budget > 0 && ix->opt_coherent_budget2 > 0) {
+            PCNN_CUDA(sc.get(&qlist, (size_t)nq + 32));
+            PCNN_CUDA(sc.get(&qcount, 4));
+            PCNN_CUDA(cudaMemsetAsync(qcount, 0, sizeof(int), s));
+        }
+        prof_begin(ix, s);
+        if (k <= 1) launch_coherent_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, qlist, qcount, s);
+        else if (k <= 2) launch_coherent_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, qlist, qcount, s);
+        else if (k <= 4) launch_coherent_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, qlist, qcount, s);
+        else if (k <= 8) launch_coherent_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, qlist, qcount, s);
+        else launch_coherent_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, qlist, qcount, s);
+        if (qlist) {
+            const WarpPlan wp = make_warp_plan(ix->view);
+            int nblk = (nq + WQ_WARPS - 1) / WQ_WARPS;
+            if (nblk > 148 * 4) nblk = 148 * 4;
+            knn_warp_list_kernel<<<nblk, WQ_WARPS * 32, 0, s>>>(ix->view, wp, q, stride, k, qlist, qcount, out_idx,
+                                                              out_dist, out_dist64);
+        }
         prof_end(ix, s);
     } else if (method == 1) {
         Scratch sc(s);

@@ -132,6 +132,11 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value);
  * this returns the device time of the most recent one in milliseconds (waits for it). */
 int pcnn_get_profile(const pcnn_index* index, float* main_kernel_ms);
 
+/* Diagnostics for load-balance studies: while buf_dev is not NULL the warp-coherent kNN kernel
+ * stores, for warp w of the launch, buf_dev[2w] = its start time (globaltimer, ns) and
+ * buf_dev[2w+1] = its duration in SM cycles; the buffer needs 2*ceil(nq/32) entries. */
+int pcnn_debug_warp_times(pcnn_index* index, unsigned long long* buf_dev);
+
 /* ------------------------------------------------------------------ radius search
  * Replaces, for nq queries at once, benchmark.hpp:68-71:
  *     RadiusNNResultSet rs(radius);  K?TreeRadiusNNSearch / OctreeRadiusNNSearch(...);

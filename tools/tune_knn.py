@@ -14,8 +14,13 @@ ix.set_option("profile", 1)
 dq = torch.from_numpy(qry).to(dev)
 K = 8
 ref = None
-cfgs = [("thread", 1, {"leaf_log": 1}), ("coherent l0", 4, {"coherent_leaf_log": 0}),
-        ("coherent l1", 4, {"coherent_leaf_log": 1}), ("coherent l2", 4, {"coherent_leaf_log": 2})]
+cfgs = [("thread", 1, {"leaf_log": 1})]
+cfgs.append(("coh l1 b150/300", 4, {"coherent_leaf_log": 1, "coherent_budget": 150, "coherent_budget2": 300}))
+cfgs.append(("lockstep b60", 6, {"coherent_budget": 60}))
+cfgs.append(("dfs", 7, {}))
+only = os.environ.get("TUNE_ONLY")
+if only:
+    cfgs = [c for c in cfgs if c[0].startswith(only)]
 for name, method, opts in cfgs:
     ix.set_option("method", method)
     for k_, v in opts.items():

@@ -393,7 +393,7 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: sort_queries must be 0 or 1");
         index->opt_sort_queries = value;
     } else if (!std::strcmp(name, "method")) {
-        PCNN_CHECK_ARG(value >= 0 && value <= 7, "pcnn_set_option: method must be 0..7");
+        PCNN_CHECK_ARG(value >= 0 && value <= 8, "pcnn_set_option: method must be 0..8");
         index->opt_method = value;
     } else if (!std::strcmp(name, "profile")) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: profile must be 0 or 1");
@@ -412,6 +412,9 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
     } else if (!std::strcmp(name, "coherent_budget")) {
         PCNN_CHECK_ARG(value >= 0, "pcnn_set_option: coherent_budget must be >= 0");
         index->opt_coherent_budget = value;
+    } else if (!std::strcmp(name, "sort_bits")) {
+        PCNN_CHECK_ARG(value >= 3 && value <= 30 && value % 3 == 0, "pcnn_set_option: sort_bits must be a multiple of 3 in 3..30");
+        index->opt_sort_bits = value;
     } else if (!std::strcmp(name, "coherent_budget2")) {
         PCNN_CHECK_ARG(value >= 0, "pcnn_set_option: coherent_budget2 must be >= 0");
         index->opt_coherent_budget2 = value;

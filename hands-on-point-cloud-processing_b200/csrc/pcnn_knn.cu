@@ -23,12 +23,12 @@ namespace pcnn {
 
 // ------------------------------------------------------------------ query ordering
 __global__ void query_code_kernel(const float* __restrict__ q, int nq, int stride,
-                                  const float* __restrict__ cube, unsigned* __restrict__ codes,
+                                  const float* __restrict__ cube, int bits, unsigned* __restrict__ codes,
                                   unsigned* __restrict__ perm) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nq) return;
     const float* p = q + (size_t)i * stride;
-    codes[i] = (unsigned)(morton63(p[0], p[1], p[2], cube, cube[3]) >> 33);  // top 30 bits
+    codes[i] = (unsigned)(morton63(p[0], p[1], p[2], cube, cube[3]) >> (63 - bits));  // top `bits` bits
     perm[i] = (unsigned)i;
 }
 
@@ -41,8 +41,9 @@ int sort_queries(const pcnn_index* ix, const float* q, int64_t nq, int stride, u
     PCNN_CUDA(sc.get(&p0, (size_t)n));
     PCNN_CUDA(sc.get(&p1, (size_t)n));
     PCNN_CUDA(sc.get(&hist, radix_hist_elems(n)));
-    query_code_kernel<<<(n + 255) / 256, 256, 0, s>>>(q, n, stride, ix->cube, c0, p0);
-    int where = radix_sort_pairs<unsigned>(c0, p0, c1, p1, hist, n, 30, s);
+    const int bits = ix->opt_sort_bits;
+    query_code_kernel<<<(n + 255) / 256, 256, 0, s>>>(q, n, stride, ix->cube, bits, c0, p0);
+    int where = radix_sort_pairs<unsigned>(c0, p0, c1, p1, hist, n, bits, s);
     *perm_out = where ? p1 : p0;
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
@@ -769,6 +770,191 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     }
 }
 
+// ------------------------------------------------------------------ hybrid: Morton sweep, nearest-first rescue
+// knn_lockstep_kernel's per-lane Morton-window sweep does the least box work when the Morton
+// seed is good (almost always); a lane whose sweep exceeds `budget` steps has a poor seed, and
+// finishes with knn_dfs_kernel's nearest-first walk from the root instead (groups the sweep
+// already covered, [g_lo, i), and the seed groups are skipped there).
+template <int K>
+__global__ void __launch_bounds__(KT_THREADS)
+knn_hybrid_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
+                  const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
+                  float* __restrict__ out_dist, double* __restrict__ out_dist64, int budget,
+                  unsigned long long* __restrict__ dbg) {
+    __shared__ int s_qg[KQ_DEPTH][KT_THREADS];
+    __shared__ float s_ql[KQ_DEPTH][KT_THREADS];
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x;
+    const int t = blockIdx.x * KT_THREADS + tid;
+    unsigned long long dbg_t0 = 0, dbg_c0 = 0;
+    if (dbg) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+        dbg_c0 = clock64();
+    }
+    const bool live = t < nq;
+    const int tt = live ? t : nq - 1;
+    const int qi = perm ? (int)perm[tt] : tt;
+    const float* qp = q + (size_t)qi * stride;
+    const float qxf = qp[0], qyf = qp[1], qzf = qp[2];
+    const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
+    TopK<K> tk;
+    tk.init();
+    int c_round = 0, c_scan = 0, c_ins = 0, c_steps = 0, c_resc = 0;  // diagnostics
+    if (iv.n > 0) {
+        const float INFf = __int_as_float(0x7f800000);
+        float wf = INFf;
+        int cnt = 0;
+#define KH_DRAIN()                                                                                   \
+        do {                                                                                         \
+            const int maxc = __reduce_max_sync(full, cnt);                                           \
+            for (int r = 0; r < maxc; r++) {                                                         \
+                const bool act = r < cnt && !(s_ql[r][tid] > wf);                                    \
+                if (__any_sync(full, act)) {                                                         \
+                    scan_own_group<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins); \
+                    c_scan++;                                                                        \
+                }                                                                                    \
+            }                                                                                        \
+            cnt = 0;                                                                                 \
+        } while (0)
+
+        const unsigned long long qcode = morton63(qxf, qyf, qzf, iv.cube, iv.cube[3]);
+        const int h = home_group(iv, qcode);
+        const int h0 = h > 0 ? h - 1 : 0, h1 = (h + 1 < iv.n0) ? h + 1 : iv.n0 - 1;
+        for (int g = h0; g <= h1; g++) { s_qg[cnt][tid] = g; s_ql[cnt][tid] = 0.f; cnt++; }
+        KH_DRAIN();
+        const int top = iv.nlev - 1;
+        int g_lo = 0, g_hi = iv.n0 - 1;
+        if (wf < 3.0e38f) {
+            const float r = __fmul_ru(__fsqrt_ru(wf), 1.000001f);
+            const float lx = __fsub_rd(qxf, r), ly = __fsub_rd(qyf, r), lz = __fsub_rd(qzf, r);
+            const float hx = __fadd_ru(qxf, r), hy = __fadd_ru(qyf, r), hz = __fadd_ru(qzf, r);
+            g_lo = group_before(iv, morton63(lx, ly, lz, iv.cube, iv.cube[3]));
+            g_hi = home_group(iv, morton63(hx, hy, hz, iv.cube, iv.cube[3]));
+        }
+        int i = g_lo;                                   // sweep position (mode 0)
+        int l = i == 0 ? top : min(__ffs(i) - 1, top);  // level of the current node (all modes)
+        int n = 0;                                      // current node (modes 1, 2)
+        unsigned pending = 0;
+        int mode = 0;  // 0 = Morton sweep, 1 = nearest-first: examine children, 2 = nearest-first: backtrack
+        bool done = i > g_hi;
+        int mysteps = 0;
+        while (true) {
+            c_round++;
+#pragma unroll 1
+            for (int s = 0; s < KL_WALK; s++) {
+                const bool can = !done && cnt <= KQ_DEPTH - 2;
+                if (!__any_sync(full, can)) break;
+                if (can) {
+                    mysteps++;
+                    if (mode == 0) {
+                        const int node = i >> l;
+                        const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + node);
+                        const float4 lo = __ldg(b), hi = __ldg(b + 1);
+                        const float lbf = lbsq32(boxgap_rd(lo.x, hi.x, qxf), boxgap_rd(lo.y, hi.y, qyf),
+                                                 boxgap_rd(lo.z, hi.z, qzf));
+                        const bool need = !(lbf > wf);
+                        if (need && l > 0) {
+                            l -= 1;
+                        } else {
+                            if (need && (node < h0 || node > h1)) {
+                                s_qg[cnt][tid] = node;
+                                s_ql[cnt][tid] = lbf;
+                                cnt++;
+                            }
+                            i = (node + 1) << l;
+                            l = min(__ffs(i) - 1, top);
+                            if (i > g_hi || i >= iv.n0) done = true;
+                        }
+                        if (!done && mysteps > budget && top > 0) {  // poor seed: nearest-first from the root
+                            c_resc++;
+                            mode = 1;
+                            l = top;
+                            n = 0;
+                        }
+                    } else {
+                        int L, P, far = 0;
+                        if (mode == 1) {
+                            L = l - 1;
+                            P = 2 * n;
+                        } else if (pending == 0) {
+                            done = true;
+                            L = 0;
+                            P = 0;
+                        } else {
+                            const int lp = __ffs((int)pending) - 1;
+                            pending &= pending - 1;
+                            far = (n >> (lp - l)) ^ 1;
+                            l = lp;
+                            n = far;
+                            L = lp;
+                            P = far & ~1;
+                        }
+                        if (!done) {
+                            const int cl = (int)(((long long)iv.n0 + (1LL << L) - 1) >> L);
+                            const float4* b = iv.box + 2 * ((size_t)iv.lev_off[L] + P);
+                            const float4 alo = __ldg(b), ahi = __ldg(b + 1);
+                            const float lbA = lbsq32(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
+                                                     boxgap_rd(alo.z, ahi.z, qzf));
+                            float lbB = INFf;
+                            const bool hasB = P + 1 < cl;
+                            if (hasB) {
+                                const float4 blo = __ldg(b + 2), bhi = __ldg(b + 3);
+                                lbB = lbsq32(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
+                                             boxgap_rd(blo.z, bhi.z, qzf));
+                            }
+                            if (mode == 1) {
+                                bool first1 = lbB < lbA;
+                                if (hasB && lbB == lbA)
+                                    first1 = qcode >= __ldg(iv.gcode + ((size_t)(P + 1) << L));
+                                const float lbn = first1 ? lbB : lbA, lbf2 = first1 ? lbA : lbB;
+                                const int near = P + (first1 ? 1 : 0);
+                                const bool passN = !(lbn > wf);
+                                const bool passF = !(lbf2 > wf) && lbf2 < INFf;
+                                if (L == 0) {
+                                    const int fg = near ^ 1;
+                                    // skip what the seed and the sweep already covered
+                                    if (passN && (near < h0 || near > h1) && (near < g_lo || near >= i)) {
+                                        s_qg[cnt][tid] = near; s_ql[cnt][tid] = lbn; cnt++;
+                                    }
+                                    if (passF && (fg < h0 || fg > h1) && (fg < g_lo || fg >= i)) {
+                                        s_qg[cnt][tid] = fg; s_ql[cnt][tid] = lbf2; cnt++;
+                                    }
+                                    mode = 2;
+                                } else if (passN) {
+                                    if (passF) pending |= 1u << L;
+                                    l = L;
+                                    n = near;
+                                } else {
+                                    mode = 2;
+                                }
+                            } else {
+                                const float lbv = (far & 1) ? lbB : lbA;
+                                if (!(lbv > wf)) mode = 1;
+                            }
+                        }
+                    }
+                }
+            }
+            KH_DRAIN();
+            if (!__any_sync(full, !done)) break;
+        }
+#undef KH_DRAIN
+        c_steps = mysteps;
+    }
+    if (live) write_row<K>(tk, qi, k, out_idx, out_dist, out_dist64);
+    if (dbg) {
+        const int maxsteps = __reduce_max_sync(full, c_steps);
+        const int sumsteps = __reduce_add_sync(full, c_steps);
+        const int nresc = __reduce_add_sync(full, c_resc);
+        if ((tid & 31) == 0) {
+            dbg[2 * (size_t)(t >> 5)] = dbg_t0;
+            dbg[2 * (size_t)(t >> 5) + 1] = (unsigned long long)(clock64() - dbg_c0);
+            unsigned long long* c = dbg + 2 * (size_t)((nq + 31) / 32) + 8 * (size_t)(t >> 5);
+            c[0] = maxsteps; c[1] = c_scan; c[2] = c_ins; c[3] = sumsteps; c[4] = c_round; c[5] = nresc;
+        }
+    }
+}
+
 // ------------------------------------------------------------------ brute-force tiles (TMA)
 constexpr int BF_THREADS = 128;
 constexpr int BF_TILE = 1024;  // points per stage: 16 KB
@@ -1029,6 +1215,13 @@ static void launch_dfs_k(const pcnn_index* ix, const float* q, int nq, int strid
         ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
 }
 template <int K>
+static void launch_hybrid_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
+                            int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
+    knn_hybrid_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
+        ix->view, q, nq, stride, perm, k, oi, od, od64,
+        ix->opt_coherent_budget > 0 ? ix->opt_coherent_budget : 0x7fffffff, ix->dbg_warp_times);
+}
+template <int K>
 static void launch_brute_k(const pcnn_index* ix, const float* q, int nq, int stride, int k, int32_t* oi,
                            float* od, double* od64, cudaStream_t s) {
     knn_brute_kernel<K><<<(nq + BF_THREADS - 1) / BF_THREADS, BF_THREADS, 0, s>>>(
@@ -1040,10 +1233,24 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     if (nq64 == 0) return PCNN_OK;
     const int nq = (int)nq64;
     int method = ix->opt_method;
-    if (method == 0) method = (k <= 16) ? 4 : 2;
-    if ((method == 1 || method == 3 || method == 4 || method == 5 || method == 6 || method == 7) && k > 16) method = 2;
+    if (method == 0) method = (k <= 16) ? 7 : 2;
+    if ((method == 1 || method == 3 || method == 4 || method == 5 || method == 6 || method == 7 || method == 8) && k > 16) method = 2;
     if (method == 3 && ix->n == 0) method = 1;
-    if (method == 7) {
+    if (method == 8) {
+        Scratch sc(s);
+        unsigned* perm = nullptr;
+        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+            int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+            if (rc != PCNN_OK) return rc;
+        }
+        prof_begin(ix, s);
+        if (k <= 1) launch_hybrid_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 2) launch_hybrid_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 4) launch_hybrid_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 8) launch_hybrid_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else launch_hybrid_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        prof_end(ix, s);
+    } else if (method == 7) {
         Scratch sc(s);
         unsigned* perm = nullptr;
         if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {

@@ -33,27 +33,58 @@ rs_hist(const KeyT* __restrict__ keys, int n, int shift, unsigned* __restrict__ 
     hist[(size_t)threadIdx.x * ntiles + blockIdx.x] = h[threadIdx.x];
 }
 
-// Exclusive scan of `total` counters in place, one block of 1024 threads.
+// Exclusive scan of `total` counters in place, one block of 1024 threads: tiles of 4096
+// counters (four consecutive per thread, coalesced), warp-shuffle scan inside a tile, running
+// carry across tiles.  The next tile's loads are issued before the current tile is scanned.
 static __global__ void __launch_bounds__(1024) rs_scan(unsigned* __restrict__ a, int total) {
-    __shared__ unsigned part[1024];
-    const int t = threadIdx.x;
-    const int chunk = (total + 1023) / 1024;
-    const int lo = min(t * chunk, total), hi = min(lo + chunk, total);
-    unsigned s = 0;
-    for (int i = lo; i < hi; i++) s += a[i];
-    part[t] = s;
+    __shared__ unsigned wsum[32];
+    __shared__ unsigned s_carry;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t == 0) s_carry = 0;
     __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {  // Hillis-Steele inclusive scan
-        unsigned v = (t >= d) ? part[t - d] : 0u;
+    unsigned v[4], nv[4];
+    auto load = [&](int base, unsigned* out) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int i = base + 4 * t + j;
+            out[j] = i < total ? a[i] : 0u;
+        }
+    };
+    load(0, v);
+    for (int base = 0; base < total; base += 4096) {
+        if (base + 4096 < total) load(base + 4096, nv);
+        const unsigned s01 = v[0] + v[1], s = s01 + v[2] + v[3];
+        unsigned inc = s;  // inclusive scan of the per-thread sums inside the warp
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        if (lane == 31) wsum[warp] = inc;
         __syncthreads();
-        part[t] += v;
+        if (warp == 0) {
+            unsigned w = wsum[lane], winc = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned u = __shfl_up_sync(0xffffffffu, winc, o);
+                if (lane >= o) winc += u;
+            }
+            wsum[lane] = winc - w;  // exclusive prefix of the warp sums
+        }
         __syncthreads();
-    }
-    unsigned run = part[t] - s;
-    for (int i = lo; i < hi; i++) {
-        unsigned v = a[i];
-        a[i] = run;
-        run += v;
+        const unsigned carry = s_carry;
+        unsigned run = carry + wsum[warp] + inc - s;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int i = base + 4 * t + j;
+            if (i < total) a[i] = run;
+            run += v[j];
+        }
+        __syncthreads();
+        if (t == 1023) s_carry = run;  // the last thread's running total = carry + tile sum
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 4; j++) v[j] = nv[j];
     }
 }
 

@@ -230,6 +230,8 @@ def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):
         r = tix.icp(d_src, tar_normals=d_nrm, max_iter=30, mode=mode)
         dt = time.perf_counter() - t0
         out[name] = {"iters_per_s": r["iters"] / dt, "iters": r["iters"], "ms_total": 1e3 * dt,
+                     "loop_iters_per_s": r["iters"] / (r["loop_ms"] * 1e-3) if r["loop_ms"] > 0 else None,
+                     "loop_us_per_iter": 1e3 * r["loop_ms"] / max(r["iters"], 1),
                      "rot_err_vs_truth": float(np.abs(r["T"][:3, :3] - T[:3, :3]).max()),
                      "trans_err_vs_truth": float(np.abs(r["T"][:3, 3] - T[:3, 3]).max()),
                      "timed": "whole call: source ordering + 30 fused iterations + one result read-back"}
@@ -243,6 +245,7 @@ def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):
     r = ix.icp(d_src, tar_normals=d_nrm, max_iter=30, mode=1)
     dt = time.perf_counter() - t0
     out["icp_p2plane_1M"] = {"iters_per_s": r["iters"] / dt, "iters": r["iters"], "ms_total": 1e3 * dt,
+                             "loop_us_per_iter": 1e3 * r["loop_ms"] / max(r["iters"], 1),
                              "pairs": r["pairs"], "status": r["status"]}
     return out
 
@@ -372,7 +375,7 @@ def run_gpu(args):
            "api": "pcnn_knn_host (C ABI), pinned host buffers, 3-stream chunked pipeline"}
     assert np.array_equal(h_idx, o_idx.cpu().numpy()), "host and device entry points disagree"
 
-    # ---- roofline of the dominant kernel (knn_thread_kernel<8>)
+    # ---- roofline of the dominant kernel (knn_dfs_kernel<8>)
     peak, peak_src = peaks()
     alg_bytes = N_QUERIES * (16 + 8 * K) + 16 * N_POINTS   # Q*(16+8k) + 16*N
     k_ms = float(np.mean(kern_ms))
@@ -384,7 +387,7 @@ def run_gpu(args):
             traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
-    roofline = {"bound": "hbm", "kernel": "knn_thread_kernel<8>", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "knn_dfs_kernel<8>", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": k_ms,
                 "kernel_share_of_step": k_ms / (sum(step_ms) / args.steps),

@@ -49,7 +49,8 @@ class IcpParams(C.Structure):
 
 class IcpResult(C.Structure):
     _fields_ = [("T", C.c_float * 16), ("iters", C.c_int32), ("converged", C.c_int32),
-                ("status", C.c_int32), ("last_loss", C.c_float), ("last_pairs", C.c_int64)]
+                ("status", C.c_int32), ("last_loss", C.c_float), ("last_pairs", C.c_int64),
+                ("loop_ms", C.c_float), ("reserved", C.c_int32)]
 
 
 EXPORTS = [

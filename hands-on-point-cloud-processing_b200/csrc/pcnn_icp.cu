@@ -16,6 +16,7 @@
 // and the count are carried.
 #include "pcnn_internal.cuh"
 #include "pcnn_search.cuh"
+#include "pcnn_lockstep.cuh"
 
 struct pcnn_icp_state {
     const pcnn_index* target = nullptr;
@@ -24,6 +25,7 @@ struct pcnn_icp_state {
     pcnn_icp_params prm{};
     float4* cur = nullptr;       // source cloud, current pose, Morton order, .w = global source index
     float4* nrm = nullptr;       // target normals in the index's Morton order (mode 1)
+    int* prev = nullptr;         // per source point: Morton position of its last correspondence (-1 = none)
     double* partials = nullptr;  // [nblocks][32]
     struct Dev* dev = nullptr;   // device-resident loop state
     int nblocks = 0;
@@ -239,38 +241,54 @@ __device__ __forceinline__ long long warp_max_ll(long long v) {
 }
 
 // MODE 0 = point-to-point (16 sums), 1 = point-to-plane (29 sums).
+// Blocks walk the source cloud with a grid stride (whole warps: tail lanes shadow the last
+// point and contribute nothing), each thread keeps its sums in registers across its points.
 template <int MODE, bool FUSED>
 __global__ void __launch_bounds__(ICP_THREADS)
-icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __restrict__ nrm, int n_src,
-                      float max_corres_dist, float loss_epsilon, int leaf_log, Dev* __restrict__ st,
-                      double* __restrict__ partials) {
+icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __restrict__ nrm,
+                      int* __restrict__ prev, int n_src, float max_corres_dist, float loss_epsilon,
+                      Dev* __restrict__ st, double* __restrict__ partials) {
     constexpr int NT = MODE == 0 ? 16 : 29;
     __shared__ double s_part[ICP_THREADS / 32][ICP_NS];
     __shared__ long long s_last[ICP_THREADS / 32];
     __shared__ bool s_is_last;
+    __shared__ int s_qg[LS_QDEPTH][ICP_THREADS];
+    __shared__ float s_ql[LS_QDEPTH][ICP_THREADS];
     if (st->done) return;  // uniform: loop already ended (converged / failed)
-    const int t = blockIdx.x * ICP_THREADS + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double v[NT];
 #pragma unroll
     for (int i = 0; i < NT; i++) v[i] = 0.0;
     long long last = -1;
-    if (t < n_src) {
-        float4 p = cur[t];
-        xform(st->Rd, st->td, p.x, p.y, p.z);  // pending T_delta of the previous iteration
-        cur[t] = p;
+    float Rd[9], td[3];
+#pragma unroll
+    for (int i = 0; i < 9; i++) Rd[i] = st->Rd[i];
+#pragma unroll
+    for (int i = 0; i < 3; i++) td[i] = st->td[i];
+    for (int base = blockIdx.x * ICP_THREADS; base < n_src; base += gridDim.x * ICP_THREADS) {
+        const int t = base + threadIdx.x;
+        const bool live = t < n_src;
+        const int tt = live ? t : n_src - 1;
+        float4 p = cur[tt];
+        xform(Rd, td, p.x, p.y, p.z);  // pending T_delta of the previous iteration
+        if (live) cur[t] = p;
         Best1f best;
-        nn1_thread(iv, p.x, p.y, p.z, leaf_log, best);
-        if (best.pos >= 0 && best.key < max_corres_dist) {  // gate on the SQUARED distance (:783, :936)
+        const int pp = prev[tt];
+        nn1_lockstep<ICP_THREADS>(iv, p.x, p.y, p.z, pp >= 0 ? (pp >> PCNN_GROUP_LOG) : -1, best, s_qg, s_ql,
+                                  threadIdx.x);
+        if (live) prev[t] = best.pos;
+        if (live && best.pos >= 0 && best.key < max_corres_dist) {  // gate on the SQUARED distance (:783, :936)
             const float4 qpt = __ldg(iv.pts + best.pos);
             if (MODE == 0) {
-                v[0] = p.x; v[1] = p.y; v[2] = p.z;
-                v[3] = qpt.x; v[4] = qpt.y; v[5] = qpt.z;
-                v[6] = (double)qpt.x * p.x; v[7] = (double)qpt.x * p.y; v[8] = (double)qpt.x * p.z;
-                v[9] = (double)qpt.y * p.x; v[10] = (double)qpt.y * p.y; v[11] = (double)qpt.y * p.z;
-                v[12] = (double)qpt.z * p.x; v[13] = (double)qpt.z * p.y; v[14] = (double)qpt.z * p.z;
-                v[15] = 1.0;
-                last = ((long long)__float_as_int(p.w) << 32) | (long long)(unsigned)__float_as_int(best.key);
+                v[0] += p.x; v[1] += p.y; v[2] += p.z;
+                v[3] += qpt.x; v[4] += qpt.y; v[5] += qpt.z;
+                v[6] += (double)qpt.x * p.x; v[7] += (double)qpt.x * p.y; v[8] += (double)qpt.x * p.z;
+                v[9] += (double)qpt.y * p.x; v[10] += (double)qpt.y * p.y; v[11] += (double)qpt.y * p.z;
+                v[12] += (double)qpt.z * p.x; v[13] += (double)qpt.z * p.y; v[14] += (double)qpt.z * p.z;
+                v[15] += 1.0;
+                const long long cand =
+                    ((long long)__float_as_int(p.w) << 32) | (long long)(unsigned)__float_as_int(best.key);
+                last = cand > last ? cand : last;
             } else {
                 const float4 nn = __ldg(nrm + best.pos);
                 // row of A and b in float32 exactly as written at registration.cpp:808-814
@@ -287,11 +305,11 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
 #pragma unroll
                 for (int r = 0; r < 6; r++)
 #pragma unroll
-                    for (int c = r; c < 6; c++) v[u++] = (double)a[r] * (double)a[c];
+                    for (int c = r; c < 6; c++) v[u++] += (double)a[r] * (double)a[c];
 #pragma unroll
-                for (int r = 0; r < 6; r++) v[21 + r] = (double)a[r] * (double)b;
-                v[27] = (double)b * (double)b;
-                v[28] = 1.0;
+                for (int r = 0; r < 6; r++) v[21 + r] += (double)a[r] * (double)b;
+                v[27] += (double)b * (double)b;
+                v[28] += 1.0;
             }
         }
     }
@@ -334,13 +352,31 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
     __threadfence();
     {
         const int col = threadIdx.x & 31, part = threadIdx.x >> 5;  // 4 row-strided partial sums per column
-        double s = 0.0;
-        long long m = -1;
-        for (int b = part; b < (int)gridDim.x; b += ICP_THREADS / 32) {
-            const double x = __ldcg(partials + (size_t)b * ICP_NS + col);
-            if (col == 31) { const long long xi = __double_as_longlong(x); m = xi > m ? xi : m; }
-            else s += x;
+        // fixed order whatever the timing: 8 interleaved accumulators per (column, part), then a
+        // fixed tree; the loads of one batch are independent so they overlap
+        constexpr int P4 = ICP_THREADS / 32, UN = 8;
+        double acc[UN];
+        long long mm[UN];
+#pragma unroll
+        for (int u = 0; u < UN; u++) { acc[u] = 0.0; mm[u] = -1; }
+        const int nb = (int)gridDim.x;
+        for (int b0 = part; b0 < nb; b0 += P4 * UN) {
+            double x[UN];
+#pragma unroll
+            for (int u = 0; u < UN; u++) {
+                const int b = b0 + u * P4;
+                x[u] = b < nb ? __ldcg(partials + (size_t)b * ICP_NS + col) : (col == 31 ? __longlong_as_double(-1LL) : 0.0);
+            }
+#pragma unroll
+            for (int u = 0; u < UN; u++) {
+                if (col == 31) { const long long xi = __double_as_longlong(x[u]); mm[u] = xi > mm[u] ? xi : mm[u]; }
+                else acc[u] += x[u];
+            }
         }
+        double s = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+        long long m = -1;
+#pragma unroll
+        for (int u = 0; u < UN; u++) m = mm[u] > m ? mm[u] : m;
         s_part[part][col] = (col == 31) ? __longlong_as_double(m) : s;
     }
     __syncthreads();
@@ -412,15 +448,20 @@ __global__ void icp_state_init_kernel(Dev* st, const float* __restrict__ T0) {
 
 __global__ void __launch_bounds__(128)
 nn1_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride, const unsigned* __restrict__ perm,
-           int leaf_log, int32_t* __restrict__ out_idx, float* __restrict__ out_d2) {
+           int32_t* __restrict__ out_idx, float* __restrict__ out_d2) {
+    __shared__ int s_qg[LS_QDEPTH][128];
+    __shared__ float s_ql[LS_QDEPTH][128];
     const int t = blockIdx.x * 128 + threadIdx.x;
-    if (t >= nq) return;
-    const int qi = perm ? (int)perm[t] : t;
+    const bool live = t < nq;
+    const int tt = live ? t : nq - 1;  // tail lanes shadow the last query: warps stay whole
+    const int qi = perm ? (int)perm[tt] : tt;
     const float* qp = q + (size_t)qi * stride;
     Best1f best;
-    nn1_thread(iv, qp[0], qp[1], qp[2], leaf_log, best);
-    out_idx[qi] = best.pos >= 0 ? best.idx : -1;
-    if (out_d2) out_d2[qi] = best.key;
+    nn1_lockstep<128>(iv, qp[0], qp[1], qp[2], -1, best, s_qg, s_ql, threadIdx.x);
+    if (live) {
+        out_idx[qi] = best.pos >= 0 ? best.idx : -1;
+        if (out_d2) out_d2[qi] = best.key;
+    }
 }
 
 int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq64, int stride, int32_t* out_idx,
@@ -433,7 +474,7 @@ int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
         if (rc != PCNN_OK) return rc;
     }
-    nn1_kernel<<<(nq + 127) / 128, 128, 0, s>>>(ix->view, q, nq, stride, perm, ix->opt_leaf_log, out_idx, out_d2);
+    nn1_kernel<<<(nq + 127) / 128, 128, 0, s>>>(ix->view, q, nq, stride, perm, out_idx, out_d2);
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
 }
@@ -442,6 +483,7 @@ static void icp_free(pcnn_icp_state* st) {
     if (!st) return;
     cudaFree(st->cur);
     cudaFree(st->nrm);
+    cudaFree(st->prev);
     cudaFree(st->partials);
     cudaFree(st->dev);
     delete st;
@@ -451,10 +493,9 @@ static int icp_launch_accumulate(pcnn_icp_state* st, bool fused, cudaStream_t s)
     if (st->n_src == 0) return PCNN_OK;
     const pcnn_index* ix = st->target;
     const int n = (int)st->n_src;
-    const int ll = ix->opt_leaf_log;
 #define PCNN_ICP_LAUNCH(MODE, FUSED)                                                             \
     icp_accumulate_kernel<MODE, FUSED><<<st->nblocks, ICP_THREADS, 0, s>>>(                      \
-        ix->view, st->cur, st->nrm, n, st->prm.max_corres_dist, st->prm.loss_epsilon, ll, st->dev, st->partials)
+        ix->view, st->cur, st->nrm, st->prev, n, st->prm.max_corres_dist, st->prm.loss_epsilon, st->dev, st->partials)
     if (st->prm.mode == 0) { if (fused) PCNN_ICP_LAUNCH(0, true); else PCNN_ICP_LAUNCH(0, false); }
     else { if (fused) PCNN_ICP_LAUNCH(1, true); else PCNN_ICP_LAUNCH(1, false); }
 #undef PCNN_ICP_LAUNCH
@@ -490,7 +531,9 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
     const int n = (int)n_src;
     st->nblocks = (n + ICP_THREADS - 1) / ICP_THREADS;
     if (st->nblocks < 1) st->nblocks = 1;
+    if (st->nblocks > 148 * 8) st->nblocks = 148 * 8;  // grid stride beyond 8 resident blocks per SM
     cudaError_t e = cudaMalloc(&st->cur, sizeof(float4) * (size_t)(n + 1));
+    if (e == cudaSuccess) e = cudaMalloc(&st->prev, sizeof(int) * (size_t)(n + 1));
     if (e == cudaSuccess) e = cudaMalloc(&st->partials, sizeof(double) * ICP_NS * (size_t)st->nblocks);
     if (e == cudaSuccess) e = cudaMalloc(&st->dev, sizeof(Dev));
     if (e == cudaSuccess && params->mode == 1) e = cudaMalloc(&st->nrm, sizeof(float4) * (size_t)(target->n + 1));
@@ -512,6 +555,7 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
             rc = PCNN_ERR_CUDA;
         } else {
             icp_state_init_kernel<<<1, 32, 0, s>>>(st->dev, T0);
+            e = cudaMemsetAsync(st->prev, 0xff, sizeof(int) * (size_t)(n + 1), s);  // -1: no correspondence yet
             if (n > 0) {
                 icp_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(src_dev, n, stride, (long long)src_index_base, T0, tmp);
                 unsigned* perm = nullptr;
@@ -565,6 +609,8 @@ int pcnn_icp_finish(pcnn_icp_state* st, pcnn_icp_result* out_host, pcnn_stream s
     out_host->status = h.status;
     out_host->last_loss = h.last_loss;
     out_host->last_pairs = h.last_pairs;
+    out_host->loop_ms = 0.f;
+    out_host->reserved = 0;
     return PCNN_OK;
 }
 
@@ -589,9 +635,16 @@ int pcnn_icp(const pcnn_index* target, const float* tar_normals_dev, const float
         rc = pcnn_icp_finish(st, out_host, stream);
         if (rc == PCNN_OK && params->max_iter > 0) out_host->status = 1;
     } else {
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        const bool timed = cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
+        if (timed) cudaEventRecord(e0, (cudaStream_t)stream);
         for (int it = 0; it < params->max_iter && rc == PCNN_OK; it++)
             rc = icp_launch_accumulate(st, true, (cudaStream_t)stream);  // fused update, no host sync
-        if (rc == PCNN_OK) rc = pcnn_icp_finish(st, out_host, stream);
+        if (timed) cudaEventRecord(e1, (cudaStream_t)stream);
+        if (rc == PCNN_OK) rc = pcnn_icp_finish(st, out_host, stream);  // waits for the stream
+        if (rc == PCNN_OK && timed) cudaEventElapsedTime(&out_host->loop_ms, e0, e1);
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
     }
     cudaStreamSynchronize((cudaStream_t)stream);
     icp_free(st);

@@ -17,43 +17,87 @@
 #include <cfloat>
 #include "pcnn_internal.cuh"
 #include "pcnn_warp.cuh"
+#include "pcnn_sort.cuh"
 
 namespace pcnn {
 
-template <bool FILL>
-__device__ __forceinline__ void emit_range(const IndexView& iv, int p0, int p1, int lane, double qx,
-                                           double qy, double qz, long long& run, int32_t* out_idx,
-                                           float* out_dist, double* out_dist64) {
+// float32 pre-tests around the exact double test.  s = fma(dx,dx, fma(dy,dy, dz*dz)) with
+// dx = p - q in float32 differs from the exact key by less than 2^-21 relative (three
+// roundings of the differences, three of the accumulation), so
+//     s <= t_in  = thr * (1 - 2^-20), rounded down  =>  key <= thr   (hit, no double needed)
+//     s >  t_out = thr * (1 + 2^-20), rounded up    =>  key >  thr   (miss)
+// and only the sliver in between pays for key64().  The same margins make the box tests
+// conservative: prune on lower bound > t_out, "contains" on farthest corner <= t_in.
+struct RadiusThr {
+    double thr;   // largest double whose sqrt is <= radius; < 0: nothing matches
+    float t_in;   // -1 when the float pre-tests are disabled (tiny / huge radii)
+    float t_out;
+};
+
+__device__ __forceinline__ float sq3(float ax, float ay, float az) {
+    return fmaf(ax, ax, fmaf(ay, ay, az * az));
+}
+
+template <bool FILL, bool D64>
+__device__ __forceinline__ void emit_range(const IndexView& iv, int p0, int p1, int lane, float qxf, float qyf,
+                                           float qzf, double qx, double qy, double qz, bool fast32,
+                                           long long& run, int32_t* out_idx, float* out_dist,
+                                           double* out_dist64) {
     if (FILL) {
         for (int p = p0 + lane; p < p1; p += 32) {
             const float4 pt = __ldg(iv.pts + p);
             const long long o = run + (p - p0);
             out_idx[o] = __float_as_int(pt.w);
-            if (out_dist || out_dist64) {
+            if (D64) {
                 const double d = sqrt(key64(pt.x, pt.y, pt.z, qx, qy, qz));
                 if (out_dist) out_dist[o] = (float)d;
-                if (out_dist64) out_dist64[o] = d;
+                out_dist64[o] = d;
+            } else if (out_dist) {
+                // float32 distances: sqrt of the float32 key, within 3e-7 relative of the exact
+                // value (the contract asks for 1e-6); the exact double path serves out_dist64
+                out_dist[o] = fast32 ? __fsqrt_rn(sq3(pt.x - qxf, pt.y - qyf, pt.z - qzf))
+                                     : (float)sqrt(key64(pt.x, pt.y, pt.z, qx, qy, qz));
             }
         }
     }
     run += (long long)(p1 - p0);
 }
 
-template <bool FILL>
+template <bool FILL, bool D64>
 __global__ void __launch_bounds__(WQ_WARPS * 32)
-radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, int stride, double thr,
-                   long long* __restrict__ counts, const long long* __restrict__ offsets,
-                   int32_t* __restrict__ out_idx, float* __restrict__ out_dist,
-                   double* __restrict__ out_dist64) {
+radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, int stride,
+                   const unsigned* __restrict__ perm, RadiusThr rt, long long* __restrict__ counts,
+                   const long long* __restrict__ offsets, int32_t* __restrict__ out_idx,
+                   float* __restrict__ out_dist, double* __restrict__ out_dist64) {
     __shared__ unsigned s_mask[WQ_WARPS][WQ_MAXD];
     __shared__ int s_base[WQ_WARPS][WQ_MAXD];
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int qi = blockIdx.x * WQ_WARPS + w;
-    if (qi >= nq) return;  // warp-uniform
+    const int slot = blockIdx.x * WQ_WARPS + w;
+    if (slot >= nq) return;  // warp-uniform
+    const int qi = perm ? (int)perm[slot] : slot;
     const float* qp = q + (size_t)qi * stride;
-    const double qx = (double)qp[0], qy = (double)qp[1], qz = (double)qp[2];
+    const float qxf = qp[0], qyf = qp[1], qzf = qp[2];
+    const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
+    const double thr = rt.thr;
+    const bool pre = rt.t_in >= 0.f;
     long long run = FILL ? offsets[qi] : 0;
+
+    // box classification: 0 = prune, 1 = descend, 2 = wholly inside the ball
+    auto classify = [&](const float4& lo, const float4& hi) -> int {
+        if (pre) {
+            const float gx = fmaxf(fmaxf(lo.x - qxf, qxf - hi.x), 0.f);
+            const float gy = fmaxf(fmaxf(lo.y - qyf, qyf - hi.y), 0.f);
+            const float gz = fmaxf(fmaxf(lo.z - qzf, qzf - hi.z), 0.f);
+            if (sq3(gx, gy, gz) > rt.t_out) return 0;
+            const float fx = fmaxf(qxf - lo.x, hi.x - qxf);
+            const float fy = fmaxf(qyf - lo.y, hi.y - qyf);
+            const float fz = fmaxf(qzf - lo.z, hi.z - qzf);
+            return sq3(fx, fy, fz) <= rt.t_in ? 2 : 1;
+        }
+        if (!(boxlb64(lo, hi, qx, qy, qz) <= thr)) return 0;
+        return boxub64(lo, hi, qx, qy, qz) <= thr ? 2 : 1;
+    };
 
     if (iv.n > 0 && thr >= 0.0) {
         int d = 0;
@@ -61,22 +105,21 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
         {
             const int l = wp.lvl[0];
             const int cnt = dev_level_count(iv.n0, l);
-            bool pend = false, cont = false;
+            int cls = 0;
             if (lane < cnt) {
                 const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + lane);
-                const float4 lo = __ldg(b), hi = __ldg(b + 1);
-                pend = boxlb64(lo, hi, qx, qy, qz) <= thr;
-                cont = pend && boxub64(lo, hi, qx, qy, qz) <= thr;
+                cls = classify(__ldg(b), __ldg(b + 1));
             }
-            unsigned cm = __ballot_sync(full, cont);
-            mask = __ballot_sync(full, pend && !cont);
+            unsigned cm = __ballot_sync(full, cls == 2);
+            mask = __ballot_sync(full, cls == 1);
             while (cm) {
                 const int j = __ffs((int)cm) - 1;
                 cm &= cm - 1;
                 const long long p0 = (long long)j << (l + PCNN_GROUP_LOG);
                 long long p1 = (long long)(j + 1) << (l + PCNN_GROUP_LOG);
                 if (p1 > iv.n) p1 = iv.n;
-                emit_range<FILL>(iv, (int)p0, (int)p1, lane, qx, qy, qz, run, out_idx, out_dist, out_dist64);
+                emit_range<FILL, D64>(iv, (int)p0, (int)p1, lane, qxf, qyf, qzf, qx, qy, qz, pre, run, out_idx,
+                                      out_dist, out_dist64);
             }
             if (lane == 0) s_base[w][0] = 0;
             __syncwarp();
@@ -96,22 +139,21 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
                 const int sh = wp.lvl[d] - l;
                 const int base = node << sh;
                 const int cnt = dev_level_count(iv.n0, l);
-                bool pend = false, cont = false;
+                int cls = 0;
                 if (lane < (1 << sh) && base + lane < cnt) {
                     const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + base + lane);
-                    const float4 lo = __ldg(b), hi = __ldg(b + 1);
-                    pend = boxlb64(lo, hi, qx, qy, qz) <= thr;
-                    cont = pend && boxub64(lo, hi, qx, qy, qz) <= thr;
+                    cls = classify(__ldg(b), __ldg(b + 1));
                 }
-                unsigned cm = __ballot_sync(full, cont);
-                const unsigned nm = __ballot_sync(full, pend && !cont);
+                unsigned cm = __ballot_sync(full, cls == 2);
+                const unsigned nm = __ballot_sync(full, cls == 1);
                 while (cm) {
                     const int c = __ffs((int)cm) - 1;
                     cm &= cm - 1;
                     const long long p0 = (long long)(base + c) << (l + PCNN_GROUP_LOG);
                     long long p1 = (long long)(base + c + 1) << (l + PCNN_GROUP_LOG);
                     if (p1 > iv.n) p1 = iv.n;
-                    emit_range<FILL>(iv, (int)p0, (int)p1, lane, qx, qy, qz, run, out_idx, out_dist, out_dist64);
+                    emit_range<FILL, D64>(iv, (int)p0, (int)p1, lane, qxf, qyf, qzf, qx, qy, qz, pre, run,
+                                          out_idx, out_dist, out_dist64);
                 }
                 if (lane == 0) { s_mask[w][d] = mask; s_base[w][d + 1] = base; }
                 __syncwarp();
@@ -120,22 +162,34 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
             } else {
                 const int pidx = (node << wp.leaf_pts_log) + lane;
                 const bool valid = lane < (1 << wp.leaf_pts_log) && pidx < iv.n;
+                bool hit = false;
+                float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
                 double dk = 0.0;
-                int id = 0;
+                bool have_dk = false;
+                float s = 0.f;
                 if (valid) {
-                    const float4 p = __ldg(iv.pts + pidx);
-                    dk = key64(p.x, p.y, p.z, qx, qy, qz);
-                    id = __float_as_int(p.w);
+                    p = __ldg(iv.pts + pidx);
+                    if (pre) {
+                        s = sq3(p.x - qxf, p.y - qyf, p.z - qzf);
+                        if (s <= rt.t_in) hit = true;
+                        else if (!(s > rt.t_out)) { dk = key64(p.x, p.y, p.z, qx, qy, qz); have_dk = true; hit = dk <= thr; }
+                    } else {
+                        dk = key64(p.x, p.y, p.z, qx, qy, qz);
+                        have_dk = true;
+                        hit = dk <= thr;
+                    }
                 }
-                const bool hit = valid && dk <= thr;
                 const unsigned m = __ballot_sync(full, hit);
                 if (FILL && hit) {
                     const long long o = run + __popc(m & ((1u << lane) - 1u));
-                    out_idx[o] = id;
-                    if (out_dist || out_dist64) {
+                    out_idx[o] = __float_as_int(p.w);
+                    if (!D64 && pre) {
+                        if (out_dist) out_dist[o] = __fsqrt_rn(s);
+                    } else if (D64 || out_dist) {
+                        if (!have_dk) dk = key64(p.x, p.y, p.z, qx, qy, qz);
                         const double dist = sqrt(dk);
                         if (out_dist) out_dist[o] = (float)dist;
-                        if (out_dist64) out_dist64[o] = dist;
+                        if (D64) out_dist64[o] = dist;
                     }
                 }
                 run += __popc(m);
@@ -182,6 +236,22 @@ static double radius_threshold(double r) {
     return t;
 }
 
+static RadiusThr make_thr(double radius) {
+    RadiusThr rt;
+    rt.thr = radius_threshold(radius);
+    rt.t_in = -1.f;
+    rt.t_out = 0.f;
+    if (rt.thr > 1e-30 && rt.thr < 1e30) {
+        float a = (float)(rt.thr * (1.0 - 9.5367431640625e-07));
+        if ((double)a > rt.thr * (1.0 - 9.5367431640625e-07)) a = std::nextafterf(a, 0.f);
+        float b = (float)(rt.thr * (1.0 + 9.5367431640625e-07));
+        if ((double)b < rt.thr * (1.0 + 9.5367431640625e-07)) b = std::nextafterf(b, INFINITY);
+        rt.t_in = a;
+        rt.t_out = b;
+    }
+    return rt;
+}
+
 int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int stride, double radius,
                         int64_t* out_offsets, cudaStream_t s) {
     const int nq = (int)nq64;
@@ -191,14 +261,19 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
         return PCNN_OK;
     }
     const WarpPlan wp = make_warp_plan(ix->view);
-    const double thr = radius_threshold(radius);
+    const RadiusThr rt = make_thr(radius);
+    Scratch sc(s);
+    unsigned* perm = nullptr;
+    if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {
+        int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+        if (rc != PCNN_OK) return rc;
+    }
     // counts are written into offsets[1..nq] then scanned in place into offsets[0..nq]
     long long* counts = (long long*)out_offsets + 1;
     prof_begin(ix, s);
-    radius_warp_kernel<false><<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
-        ix->view, wp, q, nq, stride, thr, counts, nullptr, nullptr, nullptr, nullptr);
+    radius_warp_kernel<false, false><<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
+        ix->view, wp, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
     prof_end(ix, s);
-    Scratch sc(s);
     long long* tmp;
     PCNN_CUDA(sc.get(&tmp, (size_t)nq + 1));
     scan_counts_kernel<<<1, 1024, 0, s>>>(counts, nq, tmp);
@@ -213,10 +288,21 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
     const int nq = (int)nq64;
     if (nq == 0) return PCNN_OK;
     const WarpPlan wp = make_warp_plan(ix->view);
-    const double thr = radius_threshold(radius);
+    const RadiusThr rt = make_thr(radius);
+    Scratch sc(s);
+    unsigned* perm = nullptr;
+    if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {
+        int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+        if (rc != PCNN_OK) return rc;
+    }
     prof_begin(ix, s);
-    radius_warp_kernel<true><<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
-        ix->view, wp, q, nq, stride, thr, nullptr, (const long long*)offsets, out_idx, out_dist, out_dist64);
+    const int grid = (nq + WQ_WARPS - 1) / WQ_WARPS;
+    if (out_dist64)
+        radius_warp_kernel<true, true><<<grid, WQ_WARPS * 32, 0, s>>>(
+            ix->view, wp, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, out_dist64);
+    else
+        radius_warp_kernel<true, false><<<grid, WQ_WARPS * 32, 0, s>>>(
+            ix->view, wp, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
     prof_end(ix, s);
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;

@@ -39,8 +39,10 @@
  *    exact-distance ties by tree visit order (resultSet.hpp:69-90); the two differ only
  *    inside an exact tie group straddling the k-th place.  Rows with fewer than k points
  *    available are padded with index -1 and distance +inf.
- *  - radius rows: every point with sqrt(d2) <= radius (inclusive, resultSet.hpp:134), in
- *    ascending original index (the reference's order is traversal order; compare as sets).
+ *  - radius rows: every point with sqrt(d2) <= radius (inclusive, resultSet.hpp:134), decided
+ *    on the exact double key; a row lists its hits in the index's own (Morton) order -- the
+ *    reference's order is its traversal order, so rows compare as sets.  out_dist64 holds the
+ *    exact sqrt(d2); the float32 out_dist is within 1e-6 relative of it.
  */
 #ifndef PCNN_H
 #define PCNN_H
@@ -143,7 +145,7 @@ int pcnn_debug_warp_times(pcnn_index* index, unsigned long long* buf_dev);
  * Two passes, CSR output.  pcnn_radius_count fills out_offsets_dev[nq+1] (exclusive scan of
  * the per-query hit counts, so out_offsets[nq] = total hits); if out_total_host is not NULL
  * the call waits for the stream and stores the total there.  pcnn_radius_fill writes the
- * hits of query i at [offsets[i], offsets[i+1]) in ascending original index. */
+ * hits of query i at [offsets[i], offsets[i+1]). */
 int pcnn_radius_count(const pcnn_index* index, const float* q_dev, int64_t nq, int stride,
                       double radius, int64_t* out_offsets_dev, int64_t* out_total_host,
                       pcnn_stream stream);
@@ -178,6 +180,9 @@ typedef struct {
     int32_t status;    /* 0 ok; 1 = an iteration had no correspondences or a singular system */
     float last_loss;
     int64_t last_pairs; /* correspondences kept in the last executed iteration */
+    float loop_ms;      /* pcnn_icp / pcnn_icp_host: device time of the iteration loop alone
+                           (CUDA events on the stream); 0 from pcnn_icp_finish */
+    int32_t reserved;
 } pcnn_icp_result;
 
 /* Whole loop on one GPU: no host synchronisation per iteration; one at the end to return

@@ -198,7 +198,8 @@ def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     # C2: radius r = 0.5, both passes timed, 200k of the 1M queries
     nq = 200_000
-    ix.radius(d_q[:1000], 0.5, dist="f32")
+    w = ix.radius(d_q[:nq], 0.5, dist="f32")  # same sizes as the timed call: no allocator growth inside it
+    del w
     torch.cuda.synchronize()
     ev0.record()
     off, idx, dist = ix.radius(d_q[:nq], 0.5, dist="f32")

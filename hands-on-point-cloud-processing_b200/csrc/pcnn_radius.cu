@@ -71,8 +71,17 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
                    float* __restrict__ out_dist, double* __restrict__ out_dist64) {
     __shared__ unsigned s_mask[WQ_WARPS][WQ_MAXD];
     __shared__ int s_base[WQ_WARPS][WQ_MAXD];
+    __shared__ int s_lvl[WQ_MAXD], s_cnt[WQ_MAXD], s_off[WQ_MAXD];  // per chain depth: level, nodes, box offset
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (threadIdx.x < WQ_MAXD) {
+        const int l = wp.lvl[threadIdx.x];
+        s_lvl[threadIdx.x] = l;
+        s_cnt[threadIdx.x] = (int)(((unsigned)iv.n0 + (1u << l) - 1u) >> l);
+        s_off[threadIdx.x] = 2 * iv.lev_off[l];
+    }
+    __syncthreads();
+    const int nd = wp.nd, leaf_log = wp.leaf_pts_log;
     const int slot = blockIdx.x * WQ_WARPS + w;
     if (slot >= nq) return;  // warp-uniform
     const int qi = perm ? (int)perm[slot] : slot;
@@ -103,11 +112,10 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
         int d = 0;
         unsigned mask;
         {
-            const int l = wp.lvl[0];
-            const int cnt = dev_level_count(iv.n0, l);
+            const int l = s_lvl[0];
             int cls = 0;
-            if (lane < cnt) {
-                const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + lane);
+            if (lane < s_cnt[0]) {
+                const float4* b = iv.box + (size_t)s_off[0] + 2 * lane;
                 cls = classify(__ldg(b), __ldg(b + 1));
             }
             unsigned cm = __ballot_sync(full, cls == 2);
@@ -134,14 +142,13 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
             const int j = __ffs((int)mask) - 1;
             mask &= mask - 1;
             const int node = s_base[w][d] + j;
-            if (d < wp.nd - 1) {
-                const int l = wp.lvl[d + 1];
-                const int sh = wp.lvl[d] - l;
+            if (d < nd - 1) {
+                const int l = s_lvl[d + 1];
+                const int sh = s_lvl[d] - l;
                 const int base = node << sh;
-                const int cnt = dev_level_count(iv.n0, l);
                 int cls = 0;
-                if (lane < (1 << sh) && base + lane < cnt) {
-                    const float4* b = iv.box + 2 * ((size_t)iv.lev_off[l] + base + lane);
+                if (lane < (1 << sh) && base + lane < s_cnt[d + 1]) {
+                    const float4* b = iv.box + (size_t)s_off[d + 1] + 2 * (size_t)(base + lane);
                     cls = classify(__ldg(b), __ldg(b + 1));
                 }
                 unsigned cm = __ballot_sync(full, cls == 2);
@@ -160,8 +167,8 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
                 d++;
                 mask = nm;
             } else {
-                const int pidx = (node << wp.leaf_pts_log) + lane;
-                const bool valid = lane < (1 << wp.leaf_pts_log) && pidx < iv.n;
+                const int pidx = (node << leaf_log) + lane;
+                const bool valid = lane < (1 << leaf_log) && pidx < iv.n;
                 bool hit = false;
                 float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
                 double dk = 0.0;
@@ -199,30 +206,61 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
     if (!FILL && lane == 0) counts[qi] = run;
 }
 
-// Exclusive scan of nq counts into offsets[nq+1] (one block; counts may alias offsets).
+// Exclusive scan of nq counts into offsets[nq+1] (one block of 1024 threads): tiles of 4096
+// counts, four consecutive per thread, warp-shuffle scan inside a tile, running carry across
+// tiles; the next tile is loaded before the current one is scanned.
 __global__ void __launch_bounds__(1024) scan_counts_kernel(const long long* __restrict__ counts, int nq,
                                                            long long* __restrict__ offsets) {
-    __shared__ long long part[1024];
-    const int t = threadIdx.x;
-    const int chunk = (nq + 1023) / 1024;
-    const int lo = min(t * chunk, nq), hi = min(lo + chunk, nq);
-    long long s = 0;
-    for (int i = lo; i < hi; i++) s += counts[i];
-    part[t] = s;
+    __shared__ long long wsum[32];
+    __shared__ long long s_carry;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t == 0) s_carry = 0;
     __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {
-        long long v = (t >= d) ? part[t - d] : 0;
+    long long v[4], nv[4] = {0, 0, 0, 0};
+    auto load = [&](int base, long long* out) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int i = base + 4 * t + j;
+            out[j] = i < nq ? counts[i] : 0;
+        }
+    };
+    load(0, v);
+    for (int base = 0; base < nq; base += 4096) {
+        if (base + 4096 < nq) load(base + 4096, nv);
+        const long long s = (v[0] + v[1]) + (v[2] + v[3]);
+        long long inc = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        if (lane == 31) wsum[warp] = inc;
         __syncthreads();
-        part[t] += v;
+        if (warp == 0) {
+            const long long wv = wsum[lane];
+            long long winc = wv;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long u = __shfl_up_sync(0xffffffffu, winc, o);
+                if (lane >= o) winc += u;
+            }
+            wsum[lane] = winc - wv;
+        }
         __syncthreads();
+        long long run = s_carry + wsum[warp] + inc - s;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int i = base + 4 * t + j;
+            if (i < nq) offsets[i] = run;
+            run += v[j];
+        }
+        __syncthreads();
+        if (t == 1023) s_carry = run;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 4; j++) v[j] = nv[j];
     }
-    long long run = part[t] - s;
-    for (int i = lo; i < hi; i++) {
-        long long c = counts[i];
-        offsets[i] = run;
-        run += c;
-    }
-    if (t == 1023) offsets[nq] = part[1023];
+    if (t == 0) offsets[nq] = s_carry;
 }
 
 // Largest double t with sqrt(t) <= r under IEEE rounding; -1 if nothing can match.
@@ -268,16 +306,13 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
         int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
         if (rc != PCNN_OK) return rc;
     }
-    // counts are written into offsets[1..nq] then scanned in place into offsets[0..nq]
-    long long* counts = (long long*)out_offsets + 1;
+    long long* counts;
+    PCNN_CUDA(sc.get(&counts, (size_t)nq + 1));
     prof_begin(ix, s);
     radius_warp_kernel<false, false><<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
-        ix->view, wp, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
+            ix->view, wp, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
     prof_end(ix, s);
-    long long* tmp;
-    PCNN_CUDA(sc.get(&tmp, (size_t)nq + 1));
-    scan_counts_kernel<<<1, 1024, 0, s>>>(counts, nq, tmp);
-    PCNN_CUDA(cudaMemcpyAsync(out_offsets, tmp, sizeof(int64_t) * ((size_t)nq + 1), cudaMemcpyDeviceToDevice, s));
+    scan_counts_kernel<<<1, 1024, 0, s>>>(counts, nq, (long long*)out_offsets);
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
 }

@@ -24,6 +24,7 @@ struct pcnn_index {
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;  // bracket the last build
     // query-side options (pcnn_set_option)
     int opt_sort_queries = 1;
+    int opt_radius_leaf_level = 2;  // radius search: a leaf is 8 << this points (32-point chunks)
     int opt_sort_bits = 30;  // leading Morton bits the query batch is ordered by (multiple of 3, <= 30)
     int opt_method = 0;
     int opt_leaf_log = 1;       // thread-per-query leaf = 2^leaf_log groups

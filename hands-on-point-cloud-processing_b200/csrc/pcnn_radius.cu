@@ -167,39 +167,44 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
                 d++;
                 mask = nm;
             } else {
-                const int pidx = (node << leaf_log) + lane;
-                const bool valid = lane < (1 << leaf_log) && pidx < iv.n;
-                bool hit = false;
-                float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-                double dk = 0.0;
-                bool have_dk = false;
-                float s = 0.f;
-                if (valid) {
-                    p = __ldg(iv.pts + pidx);
-                    if (pre) {
-                        s = sq3(p.x - qxf, p.y - qyf, p.z - qzf);
-                        if (s <= rt.t_in) hit = true;
-                        else if (!(s > rt.t_out)) { dk = key64(p.x, p.y, p.z, qx, qy, qz); have_dk = true; hit = dk <= thr; }
-                    } else {
-                        dk = key64(p.x, p.y, p.z, qx, qy, qz);
-                        have_dk = true;
-                        hit = dk <= thr;
+                // a leaf is 2^leaf_log points: chunks of 32, one point per lane
+                const int pbase0 = node << leaf_log;
+                const int pend = min(pbase0 + (1 << leaf_log), iv.n);
+                for (int pbase = pbase0; pbase < pend; pbase += 32) {
+                    const int pidx = pbase + lane;
+                    const bool valid = pidx < pend;
+                    bool hit = false;
+                    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+                    double dk = 0.0;
+                    bool have_dk = false;
+                    float s = 0.f;
+                    if (valid) {
+                        p = __ldg(iv.pts + pidx);
+                        if (pre) {
+                            s = sq3(p.x - qxf, p.y - qyf, p.z - qzf);
+                            if (s <= rt.t_in) hit = true;
+                            else if (!(s > rt.t_out)) { dk = key64(p.x, p.y, p.z, qx, qy, qz); have_dk = true; hit = dk <= thr; }
+                        } else {
+                            dk = key64(p.x, p.y, p.z, qx, qy, qz);
+                            have_dk = true;
+                            hit = dk <= thr;
+                        }
                     }
-                }
-                const unsigned m = __ballot_sync(full, hit);
-                if (FILL && hit) {
-                    const long long o = run + __popc(m & ((1u << lane) - 1u));
-                    out_idx[o] = __float_as_int(p.w);
-                    if (!D64 && pre) {
-                        if (out_dist) out_dist[o] = __fsqrt_rn(s);
-                    } else if (D64 || out_dist) {
-                        if (!have_dk) dk = key64(p.x, p.y, p.z, qx, qy, qz);
-                        const double dist = sqrt(dk);
-                        if (out_dist) out_dist[o] = (float)dist;
-                        if (D64) out_dist64[o] = dist;
+                    const unsigned m = __ballot_sync(full, hit);
+                    if (FILL && hit) {
+                        const long long o = run + __popc(m & ((1u << lane) - 1u));
+                        out_idx[o] = __float_as_int(p.w);
+                        if (!D64 && pre) {
+                            if (out_dist) out_dist[o] = __fsqrt_rn(s);
+                        } else if (D64 || out_dist) {
+                            if (!have_dk) dk = key64(p.x, p.y, p.z, qx, qy, qz);
+                            const double dist = sqrt(dk);
+                            if (out_dist) out_dist[o] = (float)dist;
+                            if (D64) out_dist64[o] = dist;
+                        }
                     }
+                    run += __popc(m);
                 }
-                run += __popc(m);
             }
         }
     }
@@ -298,7 +303,7 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
         PCNN_CUDA(cudaMemsetAsync(out_offsets, 0, sizeof(int64_t), s));
         return PCNN_OK;
     }
-    const WarpPlan wp = make_warp_plan(ix->view);
+    const WarpPlan wp = make_warp_plan(ix->view, ix->opt_radius_leaf_level);
     const RadiusThr rt = make_thr(radius);
     Scratch sc(s);
     unsigned* perm = nullptr;
@@ -322,7 +327,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
                        cudaStream_t s) {
     const int nq = (int)nq64;
     if (nq == 0) return PCNN_OK;
-    const WarpPlan wp = make_warp_plan(ix->view);
+    const WarpPlan wp = make_warp_plan(ix->view, ix->opt_radius_leaf_level);
     const RadiusThr rt = make_thr(radius);
     Scratch sc(s);
     unsigned* perm = nullptr;

@@ -18,10 +18,10 @@ struct WarpPlan {
 
 inline int level_count(int n0, int l) { return (int)(((long long)n0 + (1LL << l) - 1) >> l); }
 
-inline WarpPlan make_warp_plan(const IndexView& v) {
+inline WarpPlan make_warp_plan(const IndexView& v, int leaf_level = 2) {
     WarpPlan p;
     const int top = v.nlev - 1;
-    const int leaf = top < 2 ? top : 2;
+    const int leaf = top < leaf_level ? top : leaf_level;
     int chain[WQ_MAXD];
     int m = 0;
     int l = leaf;

@@ -16,7 +16,8 @@ nq = int(os.environ.get("NQ", "200000"))
 dq = torch.from_numpy(qry[:nq]).to(dev).contiguous()
 L = pc.lib()
 ref = None
-for batch, div in ((0, 1),):
+for batch, div in ((0, 2), (0, 3), (0, 4), (0, 5)):
+    ix.set_option("radius_leaf_level", div)
     for r in (0.5, 0.2, 1.0):
         best = None
         for it in range(4):

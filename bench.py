@@ -264,7 +264,7 @@ def icp_sharded(ix, pc, torch, dist, dev, nrm, qry, world, rank):
         d_nrm.copy_(torch.from_numpy(nrm))
     dist.broadcast(d_src, 0)
     dist.broadcast(d_nrm, 0)
-    lo, hi = rank * n // world, (rank + 1) * n // world
+    lo, hi = pc.shard_range(n, world, rank)
     res = None
     for iters in (2, 30):  # warm-up, then timed
         st = pc.IcpState(ix, d_src[lo:hi].contiguous(), tar_normals=d_nrm, max_iter=iters, mode=1,
@@ -275,8 +275,7 @@ def icp_sharded(ix, pc, torch, dist, dev, nrm, qry, world, rank):
         ev0.record()
         for _ in range(iters):
             st.accumulate()
-            dist.all_reduce(st.sums[:31], op=dist.ReduceOp.SUM)
-            dist.all_reduce(st.sums[31:].view(torch.int64), op=dist.ReduceOp.MAX)
+            pc.allreduce_icp_sums(st.sums, dist)
             st.update()
         ev1.record()
         torch.cuda.synchronize()

@@ -10,4 +10,5 @@ from .compat import (DistIndex, KNNResultSet, RadiusNNResultSet, kdtree_construc
                      kdtree_knn_search, kdtree_radius_search, octree_construction,
                      octree_knn_search, octree_radius_search, knn_search_batch,
                      radius_search_batch, read_velodyne_bin)
+from .sharding import shard_range, allreduce_icp_sums  # noqa: F401
 from . import synth  # noqa: F401

@@ -91,3 +91,15 @@ def hostsim():
     L.hostsim_nn1.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     L.hostsim_order.argtypes = [C.c_void_p, C.c_void_p]
     return L
+
+
+@pytest.fixture(scope="session")
+def compat_binary(tmp_path_factory):
+    """tests/compat/compat_main.cpp (a caller in the reference's own style) built against
+    include/pcnn_compat.hpp and linked with libpcnn.so."""
+    out = str(tmp_path_factory.mktemp("compat") / "compat_main")
+    pkg = os.path.join(ROOT, "hands-on-point-cloud-processing_b200")
+    subprocess.check_call(["g++", "-std=c++14", "-O2", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "compat", "compat_main.cpp"), "-o", out,
+                           "-L" + pkg, "-lpcnn", "-Wl,-rpath," + pkg])
+    return out

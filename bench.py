@@ -122,6 +122,11 @@ def cpu_oracle():
     return po.Oracle("port"), "port"
 
 
+def pc_synth():
+    import pcnn_b200 as pc
+    return pc.synth
+
+
 def cpu_knn_rate(tree, qry, cores, budget_s, chunk):
     """queries/s of the reference KD-tree loop (benchmark.hpp:59-66) split over `cores` host
     threads, on as many `chunk`-query slices of the workload as fit in ~budget_s."""
@@ -186,9 +191,30 @@ def cpu_baseline(pts, qry):
     tree.knn_checksum(qry[:2000], K, nthreads=cores)
     rate, done, dt = cpu_knn_rate(tree, qry, cores, 12.0, max(20_000, 25_000 * cores))
     rate1, done1, dt1 = cpu_knn_rate(tree, qry, 1, 3.0, 20_000)
-    return {"value": rate, "unit": "queries/s", "cores": cores, "kind": kind,
-            "sample": "first %d of the 1M queries in %.1fs on %d threads (KD-tree leaf 32, build %.2fs untimed); "
-                      "1 thread: %.3g queries/s over %d queries" % (done, dt, cores, build_s, rate1, done1)}
+    out = {"value": rate, "unit": "queries/s", "cores": cores, "kind": kind,
+           "sample": "first %d of the 1M queries in %.1fs on %d threads (KD-tree leaf 32, build %.2fs untimed); "
+                     "1 thread: %.3g queries/s over %d queries" % (done, dt, cores, build_s, rate1, done1)}
+    # the other operations of the path, same box, same clouds (bounded samples)
+    try:
+        t = time.perf_counter()
+        oc = orc.build(po.OCTREE, pts, 32, 1e-4)
+        oc_build = time.perf_counter() - t
+        nqr = 20_000
+        t = time.perf_counter()
+        oc.radius_checksum(qry[:nqr], 0.5, nthreads=cores)
+        dt_r = time.perf_counter() - t
+        out["radius_r0.5"] = {"queries_per_s": nqr / dt_r, "cores": cores, "kind": kind,
+                              "sample": "octree (leaf 32, min_extent 1e-4), first %d queries, build %.2fs untimed" % (nqr, oc_build)}
+        src, tar, tnrm, _ = pc_synth().icp_pair(100_000, seed=pc_synth().BASE_SEED + 3)
+        for mode, name in ((0, "icp_p2p_100k"), (1, "icp_p2plane_100k")):
+            t = time.perf_counter()
+            r = orc.icp(src, tar, tnrm, max_iter=10, mode=mode, accum=1, nthreads=cores)
+            dt_i = time.perf_counter() - t
+            out[name] = {"iters_per_s": r["iters"] / dt_i, "cores": cores, "kind": "port",
+                         "sample": "restated loop (nanoflann 1-NN over %d threads), %d iterations incl. one kd-tree build" % (cores, r["iters"])}
+    except Exception as exc:  # a baseline leg must never sink the bench line
+        out["extra_error"] = repr(exc)
+    return out
 
 
 def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):

@@ -955,6 +955,226 @@ knn_hybrid_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     }
 }
 
+// ------------------------------------------------------------------ nearest-first walks, 16 < k <= 32
+// Same lock-step nearest-first walk as knn_dfs_kernel; the k best of a lane do not fit its
+// registers, so they live in a binary MAX-heap in shared memory (slot-major, one column per
+// lane: conflict-free), keyed by (d2, index): the root is the k-th best = the pruning bound,
+// an accepted candidate replaces the root and sifts down (<= 5 levels for k = 32) instead of
+// shifting a sorted list, and the heap is sorted once at the end (KNNResultSet's ascending
+// order, resultSet.hpp:65-91).
+constexpr int KH_THREADS = 64;
+constexpr int KH_CAP = 32;
+
+struct HeapRef {
+    double* key;  // [KH_CAP][KH_THREADS], this lane's column
+    int* idx;
+    int k;
+    __device__ __forceinline__ double& K(int i) const { return key[i * KH_THREADS]; }
+    __device__ __forceinline__ int& I(int i) const { return idx[i * KH_THREADS]; }
+    __device__ __forceinline__ void init() const {
+        for (int i = 0; i < k; i++) { K(i) = __longlong_as_double(0x7ff0000000000000LL); I(i) = 0x7fffffff; }
+    }
+    __device__ __forceinline__ bool accepts(double d, int id) const { return kless(d, id, K(0), I(0)); }
+    // place (d, id) at position i of a heap of size n and sift it down
+    __device__ __forceinline__ void sift(int i, int n, double d, int id) const {
+        while (true) {
+            int c = 2 * i + 1;
+            if (c >= n) break;
+            double ck = K(c);
+            int ci = I(c);
+            if (c + 1 < n) {
+                const double rk = K(c + 1);
+                const int ri = I(c + 1);
+                if (kless(ck, ci, rk, ri)) { ck = rk; ci = ri; c = c + 1; }
+            }
+            if (!kless(d, id, ck, ci)) break;
+            K(i) = ck;
+            I(i) = ci;
+            i = c;
+        }
+        K(i) = d;
+        I(i) = id;
+    }
+    __device__ __forceinline__ void replace_root(double d, int id) const { sift(0, k, d, id); }
+    // heap -> ascending order in place
+    __device__ __forceinline__ void sort() const {
+        for (int n = k - 1; n > 0; n--) {
+            const double lk = K(n);
+            const int li = I(n);
+            K(n) = K(0);
+            I(n) = I(0);
+            sift(0, n, lk, li);
+        }
+    }
+};
+
+__device__ __forceinline__ void scan_own_group_heap(const IndexView& iv, int g, bool active, float qxf, float qyf,
+                                                    float qzf, double qx, double qy, double qz,
+                                                    const HeapRef& hp, float& wf) {
+    const unsigned full = 0xffffffffu;
+    const int first = g << PCNN_GROUP_LOG;
+    unsigned pass = 0;
+    if (active) {
+        const int cnt = (iv.n - first) < PCNN_GROUP ? (iv.n - first) : PCNN_GROUP;
+#pragma unroll
+        for (int j = 0; j < PCNN_GROUP; j++) {
+            if (j < cnt) {
+                const float4 p = __ldg(iv.pts + first + j);
+                const float lbf = lbsq32(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
+                if (!(lbf > wf)) pass |= 1u << j;
+            }
+        }
+    }
+    while (__any_sync(full, pass != 0)) {
+        if (pass) {
+            const int j = __ffs((int)pass) - 1;
+            pass &= pass - 1;
+            const float4 p = __ldg(iv.pts + first + j);
+            const double d = key64(p.x, p.y, p.z, qx, qy, qz);
+            const int id = __float_as_int(p.w);
+            if (hp.accepts(d, id)) {
+                hp.replace_root(d, id);
+                wf = fminf(wf, ru32(hp.K(0)));
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(KH_THREADS)
+knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
+                    const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
+                    float* __restrict__ out_dist, double* __restrict__ out_dist64) {
+    __shared__ double s_hk[KH_CAP][KH_THREADS];
+    __shared__ int s_hi[KH_CAP][KH_THREADS];
+    __shared__ int s_qg[KQ_DEPTH][KH_THREADS];
+    __shared__ float s_ql[KQ_DEPTH][KH_THREADS];
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x;
+    const int t = blockIdx.x * KH_THREADS + tid;
+    const bool live = t < nq;
+    const int tt = live ? t : nq - 1;
+    const int qi = perm ? (int)perm[tt] : tt;
+    const float* qp = q + (size_t)qi * stride;
+    const float qxf = qp[0], qyf = qp[1], qzf = qp[2];
+    const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
+    HeapRef hp;
+    hp.key = &s_hk[0][tid];
+    hp.idx = &s_hi[0][tid];
+    hp.k = k;
+    hp.init();
+    if (iv.n > 0) {
+        const float INFf = __int_as_float(0x7f800000);
+        float wf = INFf;
+        int cnt = 0;
+        const int top = iv.nlev - 1;
+        const unsigned long long qcode = morton63(qxf, qyf, qzf, iv.cube, iv.cube[3]);
+        int l = top, n = 0;
+        unsigned pending = 0;
+        int mode = 0;
+        bool done = false;
+        // seed: enough groups around the query's place on the curve to fill the heap
+        const int h = home_group(iv, qcode);
+        const int half = (k + 2 * PCNN_GROUP - 1) / (2 * PCNN_GROUP);  // groups on each side
+        const int h0 = max(h - half, 0), h1 = min(h + half, iv.n0 - 1);
+        const int nseed = __reduce_max_sync(full, (h1 - h0 + KQ_DEPTH) / KQ_DEPTH);  // same trip count in every lane
+        for (int sr = 0; sr < nseed; sr++) {
+            const int g0 = h0 + sr * KQ_DEPTH;
+            for (int g = g0; g <= h1 && g < g0 + KQ_DEPTH; g++) { s_qg[cnt][tid] = g; s_ql[cnt][tid] = 0.f; cnt++; }
+            const int maxc = __reduce_max_sync(full, cnt);
+            for (int r = 0; r < maxc; r++) {
+                const bool act = r < cnt;
+                scan_own_group_heap(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, hp, wf);
+            }
+            cnt = 0;
+        }
+        if (top == 0) done = true;
+        while (true) {
+#pragma unroll 1
+            for (int s = 0; s < KL_WALK; s++) {
+                const bool can = !done && cnt <= KQ_DEPTH - 2 && !(cnt > 0 && wf > 3.0e38f);
+                if (!__any_sync(full, can)) break;
+                if (can) {
+                    int L, P, far = 0;
+                    if (mode == 0) {
+                        L = l - 1;
+                        P = 2 * n;
+                    } else if (pending == 0) {
+                        done = true;
+                        L = 0;
+                        P = 0;
+                    } else {
+                        const int lp = __ffs((int)pending) - 1;
+                        pending &= pending - 1;
+                        far = (n >> (lp - l)) ^ 1;
+                        l = lp;
+                        n = far;
+                        L = lp;
+                        P = far & ~1;
+                    }
+                    if (!done) {
+                        const int cl = (int)(((unsigned)iv.n0 + (1u << L) - 1u) >> L);
+                        const float4* b = iv.box + 2 * ((size_t)iv.lev_off[L] + P);
+                        const float4 alo = __ldg(b), ahi = __ldg(b + 1);
+                        const float lbA = lbsq32(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
+                                                 boxgap_rd(alo.z, ahi.z, qzf));
+                        float lbB = INFf;
+                        const bool hasB = P + 1 < cl;
+                        if (hasB) {
+                            const float4 blo = __ldg(b + 2), bhi = __ldg(b + 3);
+                            lbB = lbsq32(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
+                                         boxgap_rd(blo.z, bhi.z, qzf));
+                        }
+                        if (mode == 0) {
+                            bool first1 = lbB < lbA;
+                            if (hasB && lbB == lbA) first1 = qcode >= __ldg(iv.gcode + ((size_t)(P + 1) << L));
+                            const float lbn = first1 ? lbB : lbA, lbf2 = first1 ? lbA : lbB;
+                            const int near = P + (first1 ? 1 : 0);
+                            const bool passN = !(lbn > wf);
+                            const bool passF = !(lbf2 > wf) && lbf2 < INFf;
+                            if (L == 0) {
+                                const int fg = near ^ 1;
+                                if (passN && (near < h0 || near > h1)) { s_qg[cnt][tid] = near; s_ql[cnt][tid] = lbn; cnt++; }
+                                if (passF && (fg < h0 || fg > h1)) { s_qg[cnt][tid] = fg; s_ql[cnt][tid] = lbf2; cnt++; }
+                                mode = 1;
+                            } else if (passN) {
+                                if (passF) pending |= 1u << L;
+                                l = L;
+                                n = near;
+                            } else {
+                                mode = 1;
+                            }
+                        } else {
+                            const float lbv = (far & 1) ? lbB : lbA;
+                            if (!(lbv > wf)) mode = 0;
+                        }
+                    }
+                }
+            }
+            {
+                const int maxc = __reduce_max_sync(full, cnt);
+                for (int r = 0; r < maxc; r++) {
+                    const bool act = r < cnt && !(s_ql[r][tid] > wf);
+                    if (__any_sync(full, act))
+                        scan_own_group_heap(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, hp, wf);
+                }
+                cnt = 0;
+            }
+            if (!__any_sync(full, !done)) break;
+        }
+    }
+    hp.sort();
+    if (live) {
+        for (int j = 0; j < k; j++) {
+            const int id = hp.I(j);
+            const bool have = id != 0x7fffffff;
+            const double d = have ? sqrt(hp.K(j)) : hp.K(j);
+            out_idx[(size_t)qi * k + j] = have ? id : -1;
+            if (out_dist) out_dist[(size_t)qi * k + j] = (float)d;
+            if (out_dist64) out_dist64[(size_t)qi * k + j] = d;
+        }
+    }
+}
+
 // ------------------------------------------------------------------ brute-force tiles (TMA)
 constexpr int BF_THREADS = 128;
 constexpr int BF_TILE = 1024;  // points per stage: 16 KB
@@ -1233,10 +1453,22 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     if (nq64 == 0) return PCNN_OK;
     const int nq = (int)nq64;
     int method = ix->opt_method;
-    if (method == 0) method = (k <= 16) ? 7 : 2;
+    if (method == 0) method = (k <= 16) ? 7 : (k <= KH_CAP ? 9 : 2);
+    if (method == 9 && (k > KH_CAP || ix->n == 0)) method = 2;
     if ((method == 1 || method == 3 || method == 4 || method == 5 || method == 6 || method == 7 || method == 8) && k > 16) method = 2;
     if (method == 3 && ix->n == 0) method = 1;
-    if (method == 8) {
+    if (method == 9) {
+        Scratch sc(s);
+        unsigned* perm = nullptr;
+        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+            int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+            if (rc != PCNN_OK) return rc;
+        }
+        prof_begin(ix, s);
+        knn_dfs_heap_kernel<<<(nq + KH_THREADS - 1) / KH_THREADS, KH_THREADS, 0, s>>>(
+            ix->view, q, nq, stride, perm, k, out_idx, out_dist, out_dist64);
+        prof_end(ix, s);
+    } else if (method == 8) {
         Scratch sc(s);
         unsigned* perm = nullptr;
         if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {

@@ -126,8 +126,12 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
 /* Query-side knobs (all have working defaults).  `sort_queries`: 1 = order queries along
  * the Morton curve before the search (default), 0 = caller's order, e.g. already coherent.
  * `method`: 0 = auto, 1 = thread-per-query traversal, 2 = warp-per-query traversal,
- * 3 = brute-force tiles, 4 = warp-coherent traversal (32 neighbouring queries share one
- * walk).  Returns PCNN_ERR_INVALID for unknown values. */
+ * 3 = brute-force tiles, 4 = warp-shared walk, 5 = shared walk + per-lane scan queues,
+ * 6 = lock-step Morton-window sweeps, 7 = lock-step nearest-first walks (auto for k <= 16),
+ * 8 = sweep with nearest-first rescue, 9 = nearest-first walks with a shared-memory heap
+ * (auto for 16 < k <= 32).  A method that cannot serve the requested k falls back to 2.
+ * `sort_bits` (3..30, multiple of 3): leading Morton bits the query batch is ordered by.
+ * Returns PCNN_ERR_INVALID for unknown names or values. */
 int pcnn_set_option(pcnn_index* index, const char* name, int value);
 /* With option "profile" = 1 every pcnn_knn / pcnn_radius_* call on this handle brackets its
  * main search kernel (not the query ordering) with CUDA events on the call's stream;

@@ -677,7 +677,18 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
         const int h = home_group(iv, qcode);
         const int h0 = h > 0 ? h - 1 : 0, h1 = (h + 1 < iv.n0) ? h + 1 : iv.n0 - 1;
         for (int g = h0; g <= h1; g++) { s_qg[cnt][tid] = g; s_ql[cnt][tid] = 0.f; cnt++; }
-        if (top == 0) done = true;  // a single group, already queued
+        {
+            const int maxc = __reduce_max_sync(full, cnt);
+            for (int r = 0; r < maxc; r++) {
+                const bool act = r < cnt;
+                scan_own_group<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
+            }
+            cnt = 0;
+        }
+        if (top == 0) done = true;  // a single group, already scanned
+        // start as low in the tree as the seed bound allows (usually 5-8 levels up, not 17)
+        l = walk_start_level(iv, h, qxf, qyf, qzf, wf);
+        n = h >> l;
         while (true) {
             c_round++;
 #pragma unroll 1
@@ -1088,6 +1099,8 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
             cnt = 0;
         }
         if (top == 0) done = true;
+        l = walk_start_level(iv, h, qxf, qyf, qzf, wf);
+        n = h >> l;
         while (true) {
 #pragma unroll 1
             for (int s = 0; s < KL_WALK; s++) {

@@ -47,7 +47,9 @@ __device__ __forceinline__ void nn1_lockstep(const IndexView& iv, float qx, floa
     if (seed_group < 0 || seed_group >= iv.n0) seed_group = home_group(iv, qcode);
     nn1_scan_group(iv, seed_group, qx, qy, qz, best);
     const int top = iv.nlev - 1;
-    int l = top, n = 0;
+    // start as low in the tree as the seed bound allows; with a warm start that is a few levels
+    int l = walk_start_level(iv, seed_group, qx, qy, qz, best.key);
+    int n = seed_group >> l;
     unsigned pending = 0;
     int mode = 0;  // 0 = examine the children of (l, n), 1 = backtrack
     bool done = top == 0;

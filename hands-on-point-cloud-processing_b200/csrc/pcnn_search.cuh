@@ -120,6 +120,34 @@ PCNN_HD int group_before(const IndexView& iv, unsigned long long qc) {
     return lo > 0 ? lo - 1 : 0;
 }
 
+// Lowest level at which a walk for (q, bound) may start instead of the root.  Every point within
+// sqrt(bound_f) of q lies componentwise inside [q - r, q + r]; the Morton code is monotone in
+// each coordinate, so its code lies in [code(q - r), code(q + r)].  The ancestor of group h at
+// level L holds the groups [a, a + 2^L): if every point before it has a smaller code than the
+// window and every point after it a larger one, nothing outside that subtree can matter, and
+// neither the descent from the root down to it nor its ancestors' siblings need a visit.
+// (Loads are independent across levels: one latency, not a chain.)  Returns `top` when the
+// window straddles a coarse cell boundary, or when there is no bound yet.
+#if defined(__CUDACC__)
+__device__ __forceinline__ int walk_start_level(const IndexView& iv, int h, float qxf, float qyf, float qzf,
+                                                float bound_f) {
+    const int top = iv.nlev - 1;
+    if (!(bound_f < 3.0e38f)) return top;
+    const float r = __fmul_ru(__fsqrt_ru(bound_f), 1.000001f);
+    const unsigned long long wlo = morton63(__fsub_rd(qxf, r), __fsub_rd(qyf, r), __fsub_rd(qzf, r), iv.cube, iv.cube[3]);
+    const unsigned long long whi = morton63(__fadd_ru(qxf, r), __fadd_ru(qyf, r), __fadd_ru(qzf, r), iv.cube, iv.cube[3]);
+    int Ls = top;
+    for (int L = top - 1; L >= 1; L--) {  // keeps the LOWEST level that qualifies
+        const int a = (h >> L) << L;
+        const long long b = (long long)a + (1LL << L);
+        const bool ok_lo = a == 0 || __ldg(iv.gcode + a) < wlo;
+        const bool ok_hi = b >= (long long)iv.n0 || __ldg(iv.gcode + b) > whi;
+        if (ok_lo && ok_hi) Ls = L;
+    }
+    return Ls;
+}
+#endif
+
 // Scan one 8-point group.  A float32 lower bound of d2 rejects most candidates on the FP32
 // pipe; only survivors pay for the exact double key.  wf = ru32(tk.worst()) is kept current.
 template <int K>

@@ -274,8 +274,9 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
         if (live) cur[t] = p;
         Best1f best;
         const int pp = prev[tt];
-        nn1_lockstep<ICP_THREADS>(iv, p.x, p.y, p.z, pp >= 0 ? (pp >> PCNN_GROUP_LOG) : -1, best, s_qg, s_ql,
-                                  threadIdx.x);
+        // the gate doubles as the search bound: a neighbour at or beyond it is dropped anyway
+        nn1_lockstep<ICP_THREADS>(iv, p.x, p.y, p.z, pp >= 0 ? (pp >> PCNN_GROUP_LOG) : -1, max_corres_dist, best,
+                                  s_qg, s_ql, threadIdx.x);
         if (live) prev[t] = best.pos;
         if (live && best.pos >= 0 && best.key < max_corres_dist) {  // gate on the SQUARED distance (:783, :936)
             const float4 qpt = __ldg(iv.pts + best.pos);
@@ -457,7 +458,7 @@ nn1_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride, const 
     const int qi = perm ? (int)perm[tt] : tt;
     const float* qp = q + (size_t)qi * stride;
     Best1f best;
-    nn1_lockstep<128>(iv, qp[0], qp[1], qp[2], -1, best, s_qg, s_ql, threadIdx.x);
+    nn1_lockstep<128>(iv, qp[0], qp[1], qp[2], -1, __int_as_float(0x7f800000), best, s_qg, s_ql, threadIdx.x);
     if (live) {
         out_idx[qi] = best.pos >= 0 ? best.idx : -1;
         if (out_d2) out_d2[qi] = best.key;

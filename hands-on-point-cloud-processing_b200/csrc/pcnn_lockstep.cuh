@@ -8,7 +8,8 @@
 // the farther siblings still owed a visit kept in one 32-bit mask, no stack, no recursion;
 // rounds of predicated steps instead of data-dependent loops, so a warp runs at the pace of
 // its longest walk with all its loads in flight together.  A caller that iterates (ICP) passes
-// the group its previous answer was found in: the first bound is then already (nearly) final.
+// the group its previous answer was found in: the first bound is then already (nearly) final;
+// and a caller that discards neighbours beyond a gate passes the gate as the initial bound.
 //
 // Every lane of the warp must call this together (tail lanes shadow a valid query).
 #pragma once
@@ -37,11 +38,14 @@ __device__ __forceinline__ void nn1_scan_group(const IndexView& iv, int g, float
 // s_qg / s_ql: shared-memory queues [LS_QDEPTH][THREADS], column `tid` belongs to this lane.
 template <int THREADS>
 __device__ __forceinline__ void nn1_lockstep(const IndexView& iv, float qx, float qy, float qz, int seed_group,
-                                             Best1f& best, int (*s_qg)[THREADS], float (*s_ql)[THREADS],
-                                             int tid) {
+                                             float bound, Best1f& best, int (*s_qg)[THREADS],
+                                             float (*s_ql)[THREADS], int tid) {
     const unsigned full = 0xffffffffu;
     const float INFf = __int_as_float(0x7f800000);
     best.init();
+    // `bound`: the caller only wants a neighbour with key < bound (ICP's gate on the squared
+    // distance, registration.cpp:783 / :936); farther ones may be reported as "none" (pos = -1)
+    best.key = bound;
     if (iv.n <= 0) return;
     const unsigned long long qcode = morton63(qx, qy, qz, iv.cube, iv.cube[3]);
     if (seed_group < 0 || seed_group >= iv.n0) seed_group = home_group(iv, qcode);

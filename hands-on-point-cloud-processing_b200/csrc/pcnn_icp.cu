@@ -255,7 +255,18 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
     __shared__ int s_qg[LS_QDEPTH][ICP_THREADS];
     __shared__ float s_ql[LS_QDEPTH][ICP_THREADS];
     if (st->done) return;  // uniform: loop already ended (converged / failed)
+#ifdef PCNN_ICP_TIMING
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        printf("icp timing: block 0 starts at %llu\n", t0);
+    }
+#endif
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#ifdef PCNN_ICP_TIMING
+    unsigned long long tm_a, tm_b;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_a));
+#endif
     double v[NT];
 #pragma unroll
     for (int i = 0; i < NT; i++) v[i] = 0.0;
@@ -342,6 +353,9 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
         partials[(size_t)blockIdx.x * ICP_NS + slot] = s;
     }
     // last-block-done: fold the per-block partials in a fixed order
+#ifdef PCNN_ICP_TIMING
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_b));
+#endif
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -399,7 +413,16 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
     __syncthreads();
     if (threadIdx.x == 0) {
         st->block_counter = 0;
+#ifdef PCNN_ICP_TIMING
+        unsigned long long tm_c, tm_d;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_c));
+#endif
         if (FUSED) icp_update_dev(st, MODE, loss_epsilon);
+#ifdef PCNN_ICP_TIMING
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_d));
+        printf("icp timing: last block %d: its search+reduce %llu ns, fold %llu ns, solve %llu ns\n", blockIdx.x,
+               tm_b - tm_a, tm_c - tm_b, tm_d - tm_c);
+#endif
     }
 }
 

@@ -412,6 +412,15 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
     } else if (!std::strcmp(name, "coherent_budget")) {
         PCNN_CHECK_ARG(value >= 0, "pcnn_set_option: coherent_budget must be >= 0");
         index->opt_coherent_budget = value;
+    } else if (!std::strcmp(name, "radius_batch")) {
+        PCNN_CHECK_ARG(value >= 0 && value <= 2, "pcnn_set_option: radius_batch must be 0 (never), 1 (auto) or 2 (always)");
+        index->opt_radius_batch = value;
+    } else if (!std::strcmp(name, "radius_run_div")) {
+        PCNN_CHECK_ARG(value >= 1 && value <= 1024, "pcnn_set_option: radius_run_div must be 1..1024");
+        index->opt_radius_run_div = value;
+    } else if (!std::strcmp(name, "radius_sort_bits")) {
+        PCNN_CHECK_ARG(value >= 3 && value <= 63 && value % 3 == 0, "pcnn_set_option: radius_sort_bits must be a multiple of 3 in 3..63");
+        index->opt_radius_sort_bits = value;
     } else if (!std::strcmp(name, "radius_leaf_level")) {
         PCNN_CHECK_ARG(value >= 2 && value <= 6, "pcnn_set_option: radius_leaf_level must be 2..6");
         index->opt_radius_leaf_level = value;

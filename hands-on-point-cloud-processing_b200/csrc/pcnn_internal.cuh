@@ -24,6 +24,9 @@ struct pcnn_index {
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;  // bracket the last build
     // query-side options (pcnn_set_option)
     int opt_sort_queries = 1;
+    int opt_radius_batch = 1;       // radius search, runs of neighbouring queries share one walk: 0 never, 1 auto, 2 always
+    int opt_radius_run_div = 4;     // a run spans at most radius / this per axis
+    int opt_radius_sort_bits = 45;  // leading Morton bits the batched radius search orders queries by
     int opt_radius_leaf_level = 2;  // radius search: a leaf is 8 << this points (32-point chunks)
     int opt_sort_bits = 30;  // leading Morton bits the query batch is ordered by (multiple of 3, <= 30)
     int opt_method = 0;
@@ -143,5 +146,8 @@ int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq, int stride, int
 // Morton order of a query batch: perm[i] = original id of the i-th query along the curve.
 int sort_queries(const pcnn_index* ix, const float* q, int64_t nq, int stride, unsigned** perm_out,
                  Scratch& scratch, cudaStream_t s);
+
+int sort_queries_fine(const pcnn_index* ix, const float* q, int64_t nq, int stride, int bits, unsigned** perm_out,
+                      Scratch& scratch, cudaStream_t s);
 
 }  // namespace pcnn

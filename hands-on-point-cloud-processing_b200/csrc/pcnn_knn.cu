@@ -49,6 +49,36 @@ int sort_queries(const pcnn_index* ix, const float* q, int64_t nq, int stride, u
     return PCNN_OK;
 }
 
+// Finer ordering (up to all 63 bits, 64-bit keys, one radix pass per 8 bits) for callers whose
+// work per query is large enough to pay for it: the batched radius search wants consecutive
+// queries centimetres apart, not merely in the same 15 cm cell.
+__global__ void query_code64_kernel(const float* __restrict__ q, int nq, int stride,
+                                    const float* __restrict__ cube, int bits,
+                                    unsigned long long* __restrict__ codes, unsigned* __restrict__ perm) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    const float* p = q + (size_t)i * stride;
+    codes[i] = morton63(p[0], p[1], p[2], cube, cube[3]) >> (63 - bits);
+    perm[i] = (unsigned)i;
+}
+
+int sort_queries_fine(const pcnn_index* ix, const float* q, int64_t nq, int stride, int bits, unsigned** perm_out,
+                      Scratch& sc, cudaStream_t s) {
+    const int n = (int)nq;
+    unsigned long long *c0, *c1;
+    unsigned *p0, *p1, *hist;
+    PCNN_CUDA(sc.get(&c0, (size_t)n));
+    PCNN_CUDA(sc.get(&c1, (size_t)n));
+    PCNN_CUDA(sc.get(&p0, (size_t)n));
+    PCNN_CUDA(sc.get(&p1, (size_t)n));
+    PCNN_CUDA(sc.get(&hist, radix_hist_elems(n)));
+    query_code64_kernel<<<(n + 255) / 256, 256, 0, s>>>(q, n, stride, ix->cube, bits, c0, p0);
+    int where = radix_sort_pairs<unsigned long long>(c0, p0, c1, p1, hist, n, bits, s);
+    *perm_out = where ? p1 : p0;
+    PCNN_CUDA(cudaGetLastError());
+    return PCNN_OK;
+}
+
 // ------------------------------------------------------------------ thread-per-query
 constexpr int KT_THREADS = 128;
 

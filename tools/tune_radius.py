@@ -16,9 +16,11 @@ nq = int(os.environ.get("NQ", "200000"))
 dq = torch.from_numpy(qry[:nq]).to(dev).contiguous()
 L = pc.lib()
 ref = None
-for batch, div in ((0, 2), (0, 3), (0, 4), (0, 5)):
-    ix.set_option("radius_leaf_level", div)
-    for r in (0.5, 0.2, 1.0):
+for batch, div, bits in ((0, 4, 45), (1, 2, 45), (1, 4, 45), (1, 8, 45)):
+    ix.set_option("radius_batch", batch)
+    ix.set_option("radius_run_div", div)
+    ix.set_option("radius_sort_bits", bits)
+    for r in [float(x) for x in os.environ.get('RADII', '0.5,0.2,1.0').split(',')]:
         best = None
         for it in range(4):
             off = torch.empty(nq + 1, dtype=torch.int64, device=dev)
@@ -41,5 +43,5 @@ for batch, div in ((0, 2), (0, 3), (0, 4), (0, 5)):
             if ref is None: ref = chk
             srt = "same_as_first=%s" % (chk == ref)
         alg = nq * 24 + 8 * n + 16 * len(pts)
-        print("div %d " % div + "batch %d r %.1f hits/q %.0f: count call %.3f ms (kernel %.3f)  fill call %.3f ms (kernel %.3f)  alg GB/s on kernels %.0f  %s" % (
+        print("bits %d div %d " % (bits, div) + "batch %d r %.1f hits/q %.0f: count call %.3f ms (kernel %.3f)  fill call %.3f ms (kernel %.3f)  alg GB/s on kernels %.0f  %s" % (
             batch, r, n / nq, best[0], best[1], best[2], best[3], alg / ((best[1] + best[3]) * 1e-3) / 1e9, srt or ""), flush=True)

@@ -163,6 +163,7 @@ int pcnn_radius_count(const pcnn_index* index, const float* q_dev, int64_t nq, i
     if (out_total_host) {
         PCNN_CUDA(cudaMemcpyAsync(out_total_host, out_offsets_dev + nq, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
         PCNN_CUDA(cudaStreamSynchronize(s));
+        note_radius_total(index, q_dev, nq, radius, *out_total_host);
     }
     return PCNN_OK;
 }

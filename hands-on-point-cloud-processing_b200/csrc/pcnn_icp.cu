@@ -14,6 +14,7 @@
 // SVD / 6x6 Cholesky on device.  The host never waits inside the loop.  The dense M x 6
 // matrix A of the reference is never materialised: only the 29 scalars of A^T A, A^T b, b^T b
 // and the count are carried.
+#include <type_traits>
 #include "pcnn_internal.cuh"
 #include "pcnn_search.cuh"
 #include "pcnn_lockstep.cuh"
@@ -29,6 +30,10 @@ struct pcnn_icp_state {
     double* partials = nullptr;  // [nblocks][32]
     struct Dev* dev = nullptr;   // device-resident loop state
     int nblocks = 0;
+    // device memory comes from the library's stream-ordered pool on the stream given to
+    // pcnn_icp_create and goes back to it on the same stream: no device-wide synchronisation per
+    // registration (cudaMalloc/cudaFree cost 50 ms per call next to a few GB of cached blocks)
+    cudaStream_t mem_stream = nullptr;
 };
 
 namespace pcnn {
@@ -505,11 +510,9 @@ int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
 
 static void icp_free(pcnn_icp_state* st) {
     if (!st) return;
-    cudaFree(st->cur);
-    cudaFree(st->nrm);
-    cudaFree(st->prev);
-    cudaFree(st->partials);
-    cudaFree(st->dev);
+    void* ptrs[5] = {st->cur, st->nrm, st->prev, st->partials, st->dev};
+    for (void* p : ptrs)
+        if (p) cudaFreeAsync(p, st->mem_stream);
     delete st;
 }
 
@@ -556,11 +559,19 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
     st->nblocks = (n + ICP_THREADS - 1) / ICP_THREADS;
     if (st->nblocks < 1) st->nblocks = 1;
     if (st->nblocks > 148 * 8) st->nblocks = 148 * 8;  // grid stride beyond 8 resident blocks per SM
-    cudaError_t e = cudaMalloc(&st->cur, sizeof(float4) * (size_t)(n + 1));
-    if (e == cudaSuccess) e = cudaMalloc(&st->prev, sizeof(int) * (size_t)(n + 1));
-    if (e == cudaSuccess) e = cudaMalloc(&st->partials, sizeof(double) * ICP_NS * (size_t)st->nblocks);
-    if (e == cudaSuccess) e = cudaMalloc(&st->dev, sizeof(Dev));
-    if (e == cudaSuccess && params->mode == 1) e = cudaMalloc(&st->nrm, sizeof(float4) * (size_t)(target->n + 1));
+    st->mem_stream = s;
+    cudaMemPool_t pool = lib_pool();
+    auto palloc = [&](auto** out, size_t bytes) -> cudaError_t {
+        void* p = nullptr;
+        cudaError_t err = pool ? cudaMallocFromPoolAsync(&p, bytes, pool, s) : cudaMallocAsync(&p, bytes, s);
+        *out = reinterpret_cast<std::remove_reference_t<decltype(*out)>>(p);
+        return err;
+    };
+    cudaError_t e = palloc(&st->cur, sizeof(float4) * (size_t)(n + 1));
+    if (e == cudaSuccess) e = palloc(&st->prev, sizeof(int) * (size_t)(n + 1));
+    if (e == cudaSuccess) e = palloc(&st->partials, sizeof(double) * ICP_NS * (size_t)st->nblocks);
+    if (e == cudaSuccess) e = palloc(&st->dev, sizeof(Dev));
+    if (e == cudaSuccess && params->mode == 1) e = palloc(&st->nrm, sizeof(float4) * (size_t)(target->n + 1));
     if (e != cudaSuccess) {
         set_error("pcnn_icp_create: device allocation failed: %s", cudaGetErrorString(e));
         icp_free(st);

@@ -94,7 +94,8 @@ bbox_partial(const float* __restrict__ xyz, int n, int stride, float* __restrict
     }
 }
 
-// cube[0..2] = min, cube[3] = 2^21 / side, cube[4..6] = max, cube[7] = side
+// cube[0..2] = min, cube[3] = 2^21 / side, cube[4..6] = max, cube[7] = side,
+// cube[8] = mean extent of an 8-point group (group_extent_kernel)
 __global__ void bbox_final(const float* __restrict__ partial, int nparts, float* __restrict__ cube) {
     const int a = threadIdx.x;
     if (a < 6) {
@@ -109,6 +110,37 @@ __global__ void bbox_final(const float* __restrict__ partial, int nparts, float*
         if (!(side > 0.f) || !(side < 3.0e38f)) side = 1.f;  // single point / degenerate / non-finite
         cube[7] = side;
         cube[3] = 2097152.0f / side;
+    }
+}
+
+// cube[8] = mean over a sample of <= 4096 groups of the second largest side of the group's box:
+// the scale at which the cloud is locally sampled (a surface patch of 8 points is about that
+// wide).  The run-batched radius kernels size their runs of queries with it.
+__global__ void __launch_bounds__(256) group_extent_kernel(const float4* __restrict__ box0, int n0,
+                                                           float* __restrict__ out) {
+    __shared__ float wsum[8];
+    __shared__ int wcnt[8];
+    const int samples = n0 < 4096 ? n0 : 4096;
+    float acc = 0.f;
+    int cnt = 0;
+    for (int i = threadIdx.x; i < samples; i += 256) {
+        const size_t g = (size_t)((long long)i * n0 / samples);
+        const float4 lo = box0[2 * g], hi = box0[2 * g + 1];
+        const float ex = hi.x - lo.x, ey = hi.y - lo.y, ez = hi.z - lo.z;
+        const float mid = fmaxf(fminf(ex, ey), fminf(fmaxf(ex, ey), ez));  // median of the three sides
+        if (mid == mid) { acc += mid; cnt++; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    }
+    if ((threadIdx.x & 31) == 0) { wsum[threadIdx.x >> 5] = acc; wcnt[threadIdx.x >> 5] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float a = 0.f;
+        int c = 0;
+        for (int i = 0; i < 8; i++) { a += wsum[i]; c += wcnt[i]; }
+        out[0] = c > 0 ? a / (float)c : 0.f;
     }
 }
 
@@ -169,6 +201,7 @@ __global__ void box_up(const float4* __restrict__ child, int nchild, float4* __r
 static void free_index(pcnn_index* ix) {
     if (!ix) return;
     free_host_pipe(ix->pipe);
+    if (ix->rperm) cudaFree(ix->rperm);
     cudaFree(ix->pts);
     cudaFree(ix->gcode);
     cudaFree(ix->box);
@@ -220,7 +253,7 @@ static int build_impl(pcnn_index** out, int kind, const float* xyz_dev, int64_t 
     PCNN_BUILD_CUDA(cudaMalloc(&ix->pts, sizeof(float4) * (size_t)(n0 * PCNN_GROUP + PCNN_GROUP)));
     PCNN_BUILD_CUDA(cudaMalloc(&ix->gcode, sizeof(unsigned long long) * (size_t)(n0 + 1)));
     PCNN_BUILD_CUDA(cudaMalloc(&ix->box, sizeof(float4) * 2 * nboxes));
-    PCNN_BUILD_CUDA(cudaMalloc(&ix->cube, sizeof(float) * 8));
+    PCNN_BUILD_CUDA(cudaMalloc(&ix->cube, sizeof(float) * 12));
     ix->bytes = sizeof(float4) * (size_t)(n0 * PCNN_GROUP + PCNN_GROUP) +
                 sizeof(unsigned long long) * (size_t)(n0 + 1) + sizeof(float4) * 2 * nboxes + 32;
     v.pts = ix->pts; v.gcode = ix->gcode; v.box = ix->box; v.cube = ix->cube;
@@ -256,9 +289,10 @@ static int build_impl(pcnn_index** out, int kind, const float* xyz_dev, int64_t 
                                                    ix->box + 2 * (size_t)v.lev_off[l], pc);
             cnt = pc;
         }
+        group_extent_kernel<<<1, 256, 0, s>>>(ix->box, n0, ix->cube + 8);
         PCNN_BUILD_CUDA(cudaGetLastError());
     } else {
-        PCNN_BUILD_CUDA(cudaMemsetAsync(ix->cube, 0, sizeof(float) * 8, s));
+        PCNN_BUILD_CUDA(cudaMemsetAsync(ix->cube, 0, sizeof(float) * 12, s));
         PCNN_BUILD_CUDA(cudaMemsetAsync(ix->box, 0, sizeof(float4) * 2, s));
     }
     PCNN_BUILD_CUDA(cudaEventRecord(e1, s));
@@ -413,11 +447,14 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
         PCNN_CHECK_ARG(value >= 0, "pcnn_set_option: coherent_budget must be >= 0");
         index->opt_coherent_budget = value;
     } else if (!std::strcmp(name, "radius_batch")) {
-        PCNN_CHECK_ARG(value >= 0 && value <= 2, "pcnn_set_option: radius_batch must be 0 (never), 1 (auto) or 2 (always)");
+        PCNN_CHECK_ARG(value >= 0 && value <= 5, "pcnn_set_option: radius_batch must be 0 (warp per query), 1 (auto), 2 (batched runs), 3 (lock-step), 4 (stack walk) or 5 (stack walk, batched runs)");
         index->opt_radius_batch = value;
     } else if (!std::strcmp(name, "radius_run_div")) {
-        PCNN_CHECK_ARG(value >= 1 && value <= 1024, "pcnn_set_option: radius_run_div must be 1..1024");
+        PCNN_CHECK_ARG(value >= 0 && value <= 1024, "pcnn_set_option: radius_run_div must be 0 (default per pass) or 1..1024");
         index->opt_radius_run_div = value;
+    } else if (!std::strcmp(name, "radius_run_mult_count") || !std::strcmp(name, "radius_run_mult_fill")) {
+        PCNN_CHECK_ARG(value >= 1 && value <= 100000, "pcnn_set_option: radius_run_mult_* is a percentage in 1..100000");
+        (name[16] == 'c' ? index->opt_radius_run_mult_count : index->opt_radius_run_mult_fill) = value;
     } else if (!std::strcmp(name, "radius_sort_bits")) {
         PCNN_CHECK_ARG(value >= 3 && value <= 63 && value % 3 == 0, "pcnn_set_option: radius_sort_bits must be a multiple of 3 in 3..63");
         index->opt_radius_sort_bits = value;

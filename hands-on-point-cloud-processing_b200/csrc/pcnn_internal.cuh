@@ -24,8 +24,10 @@ struct pcnn_index {
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;  // bracket the last build
     // query-side options (pcnn_set_option)
     int opt_sort_queries = 1;
-    int opt_radius_batch = 1;       // radius search, runs of neighbouring queries share one walk: 0 never, 1 auto, 2 always
-    int opt_radius_run_div = 4;     // a run spans at most radius / this per axis
+    int opt_radius_batch = 1;       // radius kernel: 0 warp per query, 1 auto, 2 batched runs, 3 lock-step (pcnn_radius.cu)
+    int opt_radius_run_div = 0;     // a run spans at most radius / this per axis; 0 = 4 for the count pass, 8 for the fill pass
+    int opt_radius_run_mult_count = 100;  // automatic run extent, percent of the mean 8-point-group extent
+    int opt_radius_run_mult_fill = 40;
     int opt_radius_sort_bits = 45;  // leading Morton bits the batched radius search orders queries by
     int opt_radius_leaf_level = 2;  // radius search: a leaf is 8 << this points (32-point chunks)
     int opt_sort_bits = 30;  // leading Morton bits the query batch is ordered by (multiple of 3, <= 30)
@@ -42,6 +44,17 @@ struct pcnn_index {
     // first use and kept for the life of the handle so a call costs no allocation
     struct HostPipe* pipe = nullptr;
     std::mutex pipe_mu;
+    // radius search: the query ordering of the last count pass, kept for the fill pass that follows
+    // it on the same stream with the same query buffer (any permutation is correct; a stale one
+    // only costs locality), and that count's hits per query (pcnn_radius.cu)
+    mutable std::mutex rperm_mu;
+    mutable unsigned* rperm = nullptr;
+    mutable size_t rperm_cap = 0;  // entries
+    mutable const float* rperm_q = nullptr;
+    mutable int rperm_nq = 0, rperm_stride = 0, rperm_kind = -1;
+    mutable cudaStream_t rperm_stream = nullptr;
+    mutable double rperm_radius = -1.0;
+    mutable double rperm_hits_per_query = -1.0;
 };
 
 namespace pcnn {
@@ -138,6 +151,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq, int stride, int
                float* out_dist, double* out_dist64, cudaStream_t s);
 int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq, int stride, double radius,
                         int64_t* out_offsets, cudaStream_t s);
+void note_radius_total(const pcnn_index* ix, const float* q, int64_t nq, double radius, int64_t total);
 int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq, int stride, double radius,
                        const int64_t* offsets, int32_t* out_idx, float* out_dist, double* out_dist64,
                        cudaStream_t s);

@@ -38,6 +38,11 @@ __device__ __forceinline__ float sq3(float ax, float ay, float az) {
     return fmaf(ax, ax, fmaf(ay, ay, az * az));
 }
 
+}  // namespace pcnn
+#include "pcnn_radius_lockstep.cuh"  // needs RadiusThr
+#include "pcnn_radius_stack.cuh"     // needs RadiusLane
+namespace pcnn {
+
 template <bool FILL, bool D64>
 __device__ __forceinline__ void emit_range(const IndexView& iv, int p0, int p1, int lane, float qxf, float qyf,
                                            float qzf, double qx, double qy, double qz, bool fast32,
@@ -55,7 +60,7 @@ __device__ __forceinline__ void emit_range(const IndexView& iv, int p0, int p1, 
             } else if (out_dist) {
                 // float32 distances: sqrt of the float32 key, within 3e-7 relative of the exact
                 // value (the contract asks for 1e-6); the exact double path serves out_dist64
-                out_dist[o] = fast32 ? __fsqrt_rn(sq3(pt.x - qxf, pt.y - qyf, pt.z - qzf))
+                out_dist[o] = fast32 ? sqrt_approx32(sq3(pt.x - qxf, pt.y - qyf, pt.z - qzf))
                                      : (float)sqrt(key64(pt.x, pt.y, pt.z, qx, qy, qz));
             }
         }
@@ -195,7 +200,7 @@ radius_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int n
                         const long long o = run + __popc(m & ((1u << lane) - 1u));
                         out_idx[o] = __float_as_int(p.w);
                         if (!D64 && pre) {
-                            if (out_dist) out_dist[o] = __fsqrt_rn(s);
+                            if (out_dist) out_dist[o] = sqrt_approx32(s);
                         } else if (D64 || out_dist) {
                             if (!have_dk) dk = key64(p.x, p.y, p.z, qx, qy, qz);
                             const double dist = sqrt(dk);
@@ -304,7 +309,7 @@ radius_batch_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int 
                             if (valid) {
                                 out_idx[ro + lane] = __float_as_int(p.w);
                                 if (!D64) {
-                                    if (out_dist) out_dist[ro + lane] = __fsqrt_rn(sq3(p.x - cx, p.y - cy, p.z - cz));
+                                    if (out_dist) out_dist[ro + lane] = sqrt_approx32(sq3(p.x - cx, p.y - cy, p.z - cz));
                                 } else {
                                     const double dist = sqrt(key64(p.x, p.y, p.z, (double)cx, (double)cy, (double)cz));
                                     if (out_dist) out_dist[ro + lane] = (float)dist;
@@ -408,7 +413,7 @@ radius_batch_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int 
                                 const long long o = ro + __popc(m & lt);
                                 out_idx[o] = id;
                                 if (!D64 && pre) {
-                                    if (out_dist) out_dist[o] = __fsqrt_rn(s);
+                                    if (out_dist) out_dist[o] = sqrt_approx32(s);
                                 } else if (D64 || out_dist) {
                                     if (!have_dk) dk = key64(p.x, p.y, p.z, (double)cx, (double)cy, (double)cz);
                                     const double dist = sqrt(dk);
@@ -427,61 +432,88 @@ radius_batch_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int 
     if (!FILL && haveq) counts[qi] = run;
 }
 
-// Exclusive scan of nq counts into offsets[nq+1] (one block of 1024 threads): tiles of 4096
-// counts, four consecutive per thread, warp-shuffle scan inside a tile, running carry across
-// tiles; the next tile is loaded before the current one is scanned.
-__global__ void __launch_bounds__(1024) scan_counts_kernel(const long long* __restrict__ counts, int nq,
-                                                           long long* __restrict__ offsets) {
-    __shared__ long long wsum[32];
-    __shared__ long long s_carry;
+// Exclusive scan of nq counts into offsets[nq+1]: tiles of 4096 counts, one block per tile, four
+// consecutive counts per thread and warp-shuffle scans inside the tile (scan_tiles_kernel writes
+// tile-local offsets and the tile's sum); one block scans the tile sums (<= 2^19 tiles for 2^31
+// queries, looped); scan_add_kernel adds each tile's base and writes offsets[nq].
+constexpr int SCAN_TILE = 4096;
+
+__device__ __forceinline__ long long block_exclusive_1024(long long s, long long* wsum, long long* total) {
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    if (t == 0) s_carry = 0;
-    __syncthreads();
-    long long v[4], nv[4] = {0, 0, 0, 0};
-    auto load = [&](int base, long long* out) {
+    long long inc = s;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int i = base + 4 * t + j;
-            out[j] = i < nq ? counts[i] : 0;
-        }
-    };
-    load(0, v);
-    for (int base = 0; base < nq; base += 4096) {
-        if (base + 4096 < nq) load(base + 4096, nv);
-        const long long s = (v[0] + v[1]) + (v[2] + v[3]);
-        long long inc = s;
+    for (int o = 1; o < 32; o <<= 1) {
+        const long long u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        const long long wv = wsum[lane];
+        long long winc = wv;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const long long u = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += u;
+            const long long u = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += u;
         }
-        if (lane == 31) wsum[warp] = inc;
-        __syncthreads();
-        if (warp == 0) {
-            const long long wv = wsum[lane];
-            long long winc = wv;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const long long u = __shfl_up_sync(0xffffffffu, winc, o);
-                if (lane >= o) winc += u;
-            }
-            wsum[lane] = winc - wv;
-        }
-        __syncthreads();
-        long long run = s_carry + wsum[warp] + inc - s;
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int i = base + 4 * t + j;
-            if (i < nq) offsets[i] = run;
-            run += v[j];
-        }
-        __syncthreads();
-        if (t == 1023) s_carry = run;
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < 4; j++) v[j] = nv[j];
+        wsum[lane] = winc - wv;
+        if (lane == 31) *total = winc;
     }
-    if (t == 0) offsets[nq] = s_carry;
+    __syncthreads();
+    return wsum[warp] + inc - s;
+}
+
+__global__ void __launch_bounds__(1024) scan_tiles_kernel(const long long* __restrict__ counts, int nq,
+                                                          long long* __restrict__ offsets,
+                                                          long long* __restrict__ tile_sums) {
+    __shared__ long long wsum[32];
+    __shared__ long long total;
+    const int base = blockIdx.x * SCAN_TILE + 4 * threadIdx.x;
+    long long v[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) v[j] = base + j < nq ? counts[base + j] : 0;
+    long long run = block_exclusive_1024((v[0] + v[1]) + (v[2] + v[3]), wsum, &total);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        if (base + j < nq) offsets[base + j] = run;
+        run += v[j];
+    }
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024) scan_sums_kernel(long long* __restrict__ tile_sums, int ntiles) {
+    __shared__ long long wsum[32];
+    __shared__ long long total;
+    long long carry = 0;
+    for (int base = 0; base < ntiles; base += 1024) {
+        const int i = base + threadIdx.x;
+        const long long v = i < ntiles ? tile_sums[i] : 0;
+        const long long ex = block_exclusive_1024(v, wsum, &total);
+        if (i < ntiles) tile_sums[i] = carry + ex;
+        carry += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) tile_sums[ntiles] = carry;
+}
+
+__global__ void __launch_bounds__(1024) scan_add_kernel(long long* __restrict__ offsets, int nq,
+                                                        const long long* __restrict__ tile_sums, int ntiles) {
+    const long long add = tile_sums[blockIdx.x];
+    const int base = blockIdx.x * SCAN_TILE + 4 * threadIdx.x;
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        if (base + j < nq) offsets[base + j] += add;
+    if (blockIdx.x == 0 && threadIdx.x == 0) offsets[nq] = tile_sums[ntiles];
+}
+
+static int scan_counts(const long long* counts, int nq, long long* offsets, Scratch& sc, cudaStream_t s) {
+    const int ntiles = (nq + SCAN_TILE - 1) / SCAN_TILE;
+    long long* tile_sums;
+    PCNN_CUDA(sc.get(&tile_sums, (size_t)ntiles + 1));
+    scan_tiles_kernel<<<ntiles, 1024, 0, s>>>(counts, nq, offsets, tile_sums);
+    scan_sums_kernel<<<1, 1024, 0, s>>>(tile_sums, ntiles);
+    scan_add_kernel<<<ntiles, 1024, 0, s>>>(offsets, nq, tile_sums, ntiles);
+    return PCNN_OK;
 }
 
 // Largest double t with sqrt(t) <= r under IEEE rounding; -1 if nothing can match.
@@ -511,14 +543,75 @@ static RadiusThr make_thr(double radius) {
     return rt;
 }
 
-// The batched form pays off when neighbours in the ordered batch are close compared with the
-// radius, i.e. when the batch is about as dense as the cloud (measured: 1M queries on the 1M
-// cloud 9.3 -> 6.5 ms at r = 0.5; a 200k subset of the same queries 1.8 -> 2.5 ms).  Option
-// radius_batch: 0 = never, 1 = automatic, 2 = always.  Count and fill take the same decision.
-static bool use_batch(const pcnn_index* ix, int nq, double radius) {
-    if (!(radius > 1e-12 && radius < 1e12) || ix->opt_radius_batch == 0) return false;
-    if (ix->opt_radius_batch == 2) return true;
-    return ix->opt_sort_queries && nq > 1024 && 2 * (int64_t)nq >= ix->n;
+// Which kernel serves a call (option radius_batch; the two passes decide independently, every
+// kernel finds the same set):
+//   0 = one warp per query, depth first (radius_warp_kernel), 2 = runs of neighbouring queries
+//   share one depth-first walk (radius_batch_kernel), 3 = one query per lane, warp-wide writes
+//   (radius_lockstep_kernel), 4 = one warp per query, dense stack walk (radius_stack_kernel),
+//   5 = dense stack walk shared by a run of queries (radius_stack_batch_kernel),
+//   1 = automatic.  Measured on the 1M aggregate (count + fill kernels, ms):
+//       1M queries r=0.5:  0: 3.76+5.34   2: 2.05+4.23   3: 2.86+6.47   4: 3.34+4.90   5: 1.28+3.72
+//       1M queries r=1.0:  0: 7.27+12.7   2: 3.86+16.7                  4: 5.91+11.5   5: 2.33+14.8
+//       200k queries r=0.5: 0: 0.75+1.04  2: 0.82+1.54  3: 0.80+2.06    4: 0.65+0.94   5: 0.60+1.27
+//   so: a batch about as dense as the cloud shares walks (5), except that a fill with thousands
+//   of hits per query is dominated by contained subtrees, which the per-query kernel (4) writes
+//   with less overhead; sparse batches use 4.
+enum { RM_WARP = 0, RM_BATCH = 2, RM_LOCKSTEP = 3, RM_STACK = 4, RM_STACK_BATCH = 5 };
+static int radius_method(const pcnn_index* ix, int nq, double radius, bool fill, double hits_per_query) {
+    int m = ix->opt_radius_batch;
+    if (m == 1) {
+        const bool dense = ix->opt_sort_queries && nq > 1024 && 2 * (int64_t)nq >= ix->n;
+        m = dense ? RM_STACK_BATCH : RM_STACK;
+        if (fill && hits_per_query > 2000.0) m = RM_STACK;
+    }
+    if (m == RM_BATCH && !(radius > 1e-12 && radius < 1e12)) m = RM_WARP;
+    if (m == RM_STACK_BATCH && !(radius > 1e-12 && radius < 1e12)) m = RM_STACK;
+    if ((m == RM_LOCKSTEP || m == RM_STACK || m == RM_STACK_BATCH) && ix->view.n0 >= RL_MAX_GROUPS) m = RM_WARP;  // 27-bit node fields
+    return m;
+}
+// run extent handed to the run-batched kernels: radius / radius_run_div when the option is set,
+// else negative = "that many mean group extents" (pcnn_radius_stack.cuh)
+static float run_extent(const pcnn_index* ix, double radius, bool fill, bool stack) {
+    if (ix->opt_radius_run_div > 0) return (float)(radius / ix->opt_radius_run_div);
+    if (!stack) return (float)(radius / 4);
+    return -0.01f * (float)(fill ? ix->opt_radius_run_mult_fill : ix->opt_radius_run_mult_count);
+}
+
+// The fill pass reuses the query ordering of the count pass before it (same stream, same query
+// buffer, same kind of ordering).  Any permutation of the queries is correct -- the ordering
+// only buys locality -- so a stale one cannot change a result.
+static void remember_perm(const pcnn_index* ix, const unsigned* perm, const float* q, int nq, int stride, int kind,
+                          double radius, cudaStream_t s) {
+    std::lock_guard<std::mutex> lk(ix->rperm_mu);
+    ix->rperm_kind = -1;
+    ix->rperm_hits_per_query = -1.0;
+    if (!perm) return;
+    if ((size_t)nq > ix->rperm_cap) {
+        if (ix->rperm) cudaFree(ix->rperm);
+        ix->rperm = nullptr;
+        ix->rperm_cap = 0;
+        if (cudaMalloc(&ix->rperm, (size_t)nq * sizeof(unsigned)) != cudaSuccess) { cudaGetLastError(); return; }
+        ix->rperm_cap = (size_t)nq;
+    }
+    if (cudaMemcpyAsync(ix->rperm, perm, (size_t)nq * sizeof(unsigned), cudaMemcpyDeviceToDevice, s) != cudaSuccess) return;
+    ix->rperm_q = q; ix->rperm_nq = nq; ix->rperm_stride = stride; ix->rperm_kind = kind;
+    ix->rperm_stream = s; ix->rperm_radius = radius;
+}
+static const unsigned* recall_perm(const pcnn_index* ix, const float* q, int nq, int stride, int kind, cudaStream_t s) {
+    std::lock_guard<std::mutex> lk(ix->rperm_mu);
+    if (ix->rperm && ix->rperm_kind == kind && ix->rperm_q == q && ix->rperm_nq == nq && ix->rperm_stride == stride &&
+        ix->rperm_stream == s)
+        return ix->rperm;
+    return nullptr;
+}
+void note_radius_total(const pcnn_index* ix, const float* q, int64_t nq, double radius, int64_t total) {
+    std::lock_guard<std::mutex> lk(ix->rperm_mu);
+    if (ix->rperm_q == q && ix->rperm_nq == (int)nq && ix->rperm_radius == radius && nq > 0)
+        ix->rperm_hits_per_query = (double)total / (double)nq;
+}
+static double recall_hits(const pcnn_index* ix, const float* q, int nq, double radius) {
+    std::lock_guard<std::mutex> lk(ix->rperm_mu);
+    return (ix->rperm_q == q && ix->rperm_nq == nq && ix->rperm_radius == radius) ? ix->rperm_hits_per_query : -1.0;
 }
 
 int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int stride, double radius,
@@ -533,26 +626,39 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
     const RadiusThr rt = make_thr(radius);
     Scratch sc(s);
     unsigned* perm = nullptr;
-    const bool batch = use_batch(ix, nq, radius);
+    const int method = radius_method(ix, nq, radius, false, -1.0);
+    const bool batch = method == RM_BATCH || method == RM_STACK_BATCH;
     if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {
         int rc = batch ? sort_queries_fine(ix, q, nq, stride, ix->opt_radius_sort_bits, &perm, sc, s)
                        : sort_queries(ix, q, nq, stride, &perm, sc, s);
         if (rc != PCNN_OK) return rc;
     }
+    remember_perm(ix, perm, q, nq, stride, batch ? 1 : 0, radius, s);
     long long* counts;
     PCNN_CUDA(sc.get(&counts, (size_t)nq + 1));
     prof_begin(ix, s);
-    if (batch) {
+    if (method == RM_STACK_BATCH) {
+        const int nwarps = (nq + 31) / 32;
+        radius_stack_batch_kernel<false, false><<<(nwarps + RK_WARPS - 1) / RK_WARPS, RK_WARPS * 32, 0, s>>>(
+            ix->view, q, nq, stride, perm, rt, run_extent(ix, radius, false, true), (float)radius, counts, nullptr,
+            nullptr, nullptr, nullptr);
+    } else if (method == RM_STACK) {
+        radius_stack_kernel<false, false><<<(nq + RK_WARPS - 1) / RK_WARPS, RK_WARPS * 32, 0, s>>>(
+            ix->view, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
+    } else if (method == RM_LOCKSTEP) {
+        radius_lockstep_kernel<false, false><<<(nq + RL_THREADS - 1) / RL_THREADS, RL_THREADS, 0, s>>>(
+            ix->view, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
+    } else if (batch) {
         const int nwarps = (nq + 31) / 32;
         radius_batch_kernel<false, false><<<(nwarps + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
-            ix->view, wp, q, nq, stride, perm, rt, (float)(radius / ix->opt_radius_run_div), counts, nullptr, nullptr,
+            ix->view, wp, q, nq, stride, perm, rt, run_extent(ix, radius, false, false), counts, nullptr, nullptr,
             nullptr, nullptr);
     } else {
         radius_warp_kernel<false, false><<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
             ix->view, wp, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
     }
     prof_end(ix, s);
-    scan_counts_kernel<<<1, 1024, 0, s>>>(counts, nq, (long long*)out_offsets);
+    if (int rc = scan_counts(counts, nq, (long long*)out_offsets, sc, s)) return rc;
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
 }
@@ -566,17 +672,60 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
     const RadiusThr rt = make_thr(radius);
     Scratch sc(s);
     unsigned* perm = nullptr;
-    const bool batch = use_batch(ix, nq, radius);
+    const int method = radius_method(ix, nq, radius, true, recall_hits(ix, q, nq, radius));
+    const bool batch = method == RM_BATCH || method == RM_STACK_BATCH;
     if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {
-        int rc = batch ? sort_queries_fine(ix, q, nq, stride, ix->opt_radius_sort_bits, &perm, sc, s)
-                       : sort_queries(ix, q, nq, stride, &perm, sc, s);
-        if (rc != PCNN_OK) return rc;
+        perm = const_cast<unsigned*>(recall_perm(ix, q, nq, stride, batch ? 1 : 0, s));
+        if (!perm) {
+            int rc = batch ? sort_queries_fine(ix, q, nq, stride, ix->opt_radius_sort_bits, &perm, sc, s)
+                           : sort_queries(ix, q, nq, stride, &perm, sc, s);
+            if (rc != PCNN_OK) return rc;
+        }
     }
     prof_begin(ix, s);
+    if (method == RM_STACK_BATCH) {
+        const int nwarps = (nq + 31) / 32;
+        const int bgrid = (nwarps + RK_WARPS - 1) / RK_WARPS;
+        const float ext = run_extent(ix, radius, true, true);
+        if (out_dist64)
+            radius_stack_batch_kernel<true, true><<<bgrid, RK_WARPS * 32, 0, s>>>(
+                ix->view, q, nq, stride, perm, rt, ext, (float)radius, nullptr, (const long long*)offsets, out_idx, out_dist,
+                out_dist64);
+        else
+            radius_stack_batch_kernel<true, false><<<bgrid, RK_WARPS * 32, 0, s>>>(
+                ix->view, q, nq, stride, perm, rt, ext, (float)radius, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
+        prof_end(ix, s);
+        PCNN_CUDA(cudaGetLastError());
+        return PCNN_OK;
+    }
+    if (method == RM_STACK) {
+        const int sgrid = (nq + RK_WARPS - 1) / RK_WARPS;
+        if (out_dist64)
+            radius_stack_kernel<true, true><<<sgrid, RK_WARPS * 32, 0, s>>>(
+                ix->view, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, out_dist64);
+        else
+            radius_stack_kernel<true, false><<<sgrid, RK_WARPS * 32, 0, s>>>(
+                ix->view, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
+        prof_end(ix, s);
+        PCNN_CUDA(cudaGetLastError());
+        return PCNN_OK;
+    }
+    if (method == RM_LOCKSTEP) {
+        const int lgrid = (nq + RL_THREADS - 1) / RL_THREADS;
+        if (out_dist64)
+            radius_lockstep_kernel<true, true><<<lgrid, RL_THREADS, 0, s>>>(
+                ix->view, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, out_dist64);
+        else
+            radius_lockstep_kernel<true, false><<<lgrid, RL_THREADS, 0, s>>>(
+                ix->view, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
+        prof_end(ix, s);
+        PCNN_CUDA(cudaGetLastError());
+        return PCNN_OK;
+    }
     if (batch) {
         const int nwarps = (nq + 31) / 32;
         const int bgrid = (nwarps + WQ_WARPS - 1) / WQ_WARPS;
-        const float ext = (float)(radius / ix->opt_radius_run_div);
+        const float ext = run_extent(ix, radius, true, false);
         if (out_dist64)
             radius_batch_kernel<true, true><<<bgrid, WQ_WARPS * 32, 0, s>>>(
                 ix->view, wp, q, nq, stride, perm, rt, ext, nullptr, (const long long*)offsets, out_idx, out_dist, out_dist64);

@@ -16,13 +16,21 @@ nq = int(os.environ.get("NQ", "200000"))
 dq = torch.from_numpy(qry[:nq]).to(dev).contiguous()
 L = pc.lib()
 ref = None
-for batch, div, bits in ((0, 4, 45), (1, 2, 45), (1, 4, 45), (1, 8, 45)):
+cfgs = ((0, 4, 45), (2, 4, 45), (3, 4, 45), (4, 4, 45))
+if os.environ.get("CFG"):  # e.g. CFG="1,4,45;0,4,45"
+    cfgs = tuple(tuple(int(v) for v in c.split(",")) for c in os.environ["CFG"].split(";"))
+iters = int(os.environ.get("ITERS", "4"))
+for batch, div, bits in cfgs:
     ix.set_option("radius_batch", batch)
     ix.set_option("radius_run_div", div)
     ix.set_option("radius_sort_bits", bits)
+    if os.environ.get("MULT"):  # "count,fill" percentages of the mean group extent (used when div = 0)
+        mc, mf = (int(v) for v in os.environ["MULT"].split(","))
+        ix.set_option("radius_run_mult_count", mc)
+        ix.set_option("radius_run_mult_fill", mf)
     for r in [float(x) for x in os.environ.get('RADII', '0.5,0.2,1.0').split(',')]:
         best = None
-        for it in range(4):
+        for it in range(iters):
             off = torch.empty(nq + 1, dtype=torch.int64, device=dev)
             total = C.c_int64(0)
             torch.cuda.synchronize(); t0 = time.perf_counter()

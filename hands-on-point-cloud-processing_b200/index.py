@@ -102,7 +102,8 @@ class Index:
         """All neighbours within ``radius`` (inclusive): CSR (offsets[nq+1], idx, dist).
 
         Batched ``RadiusNNResultSet rs(r); K?TreeRadiusNNSearch(...)`` (benchmark.hpp:68-71).
-        Rows are in the index's Morton order; the reference's are in traversal order.
+        The order inside a row is deterministic but unspecified (the reference's is its own
+        traversal order): compare rows as sets.
         """
         L = lib()
         if _is_torch(q):

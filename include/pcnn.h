@@ -40,8 +40,9 @@
  *    inside an exact tie group straddling the k-th place.  Rows with fewer than k points
  *    available are padded with index -1 and distance +inf.
  *  - radius rows: every point with sqrt(d2) <= radius (inclusive, resultSet.hpp:134), decided
- *    on the exact double key; a row lists its hits in the index's own (Morton) order -- the
- *    reference's order is its traversal order, so rows compare as sets.  out_dist64 holds the
+ *    on the exact double key; the order inside a row is deterministic (the same in every call
+ *    with the same inputs and options) but unspecified -- the reference's order is its own
+ *    traversal order -- so rows compare as sets.  out_dist64 holds the
  *    exact sqrt(d2); the float32 out_dist is within 1e-6 relative of it.
  */
 #ifndef PCNN_H
@@ -131,6 +132,11 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
  * 8 = sweep with nearest-first rescue, 9 = nearest-first walks with a shared-memory heap
  * (auto for 16 < k <= 32).  A method that cannot serve the requested k falls back to 2.
  * `sort_bits` (3..30, multiple of 3): leading Morton bits the query batch is ordered by.
+ * `radius_batch`: radius kernel, 1 = auto (default), 0 = warp per query, 2 = runs of queries,
+ * 3 = query per lane, 4 = warp per query with a dense stack walk, 5 = dense stack walk per run
+ * of queries; `radius_run_div` (0 = auto), `radius_run_mult_count` / `radius_run_mult_fill`
+ * (percent of the cloud's mean 8-point-group extent) size the runs.  Every choice returns the
+ * same sets.
  * Returns PCNN_ERR_INVALID for unknown names or values. */
 int pcnn_set_option(pcnn_index* index, const char* name, int value);
 /* With option "profile" = 1 every pcnn_knn / pcnn_radius_* call on this handle brackets its

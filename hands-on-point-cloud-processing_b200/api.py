@@ -53,13 +53,18 @@ class IcpResult(C.Structure):
                 ("loop_ms", C.c_float), ("reserved", C.c_int32)]
 
 
+class IssParams(C.Structure):
+    _fields_ = [("local_radius", C.c_float), ("non_max_radius", C.c_float), ("gamma21", C.c_float),
+                ("gamma32", C.c_float), ("min_neighbors", C.c_int32), ("weighted", C.c_int32)]
+
+
 EXPORTS = [
     "pcnn_last_error", "pcnn_version", "pcnn_device_count", "pcnn_index_build",
     "pcnn_index_build_host", "pcnn_index_destroy", "pcnn_index_get_info", "pcnn_knn",
     "pcnn_knn_host", "pcnn_set_option", "pcnn_get_profile", "pcnn_radius_count", "pcnn_radius_fill",
     "pcnn_radius_host", "pcnn_icp", "pcnn_icp_host", "pcnn_icp_create", "pcnn_icp_accumulate",
     "pcnn_icp_sums_dev", "pcnn_icp_update", "pcnn_icp_finish", "pcnn_icp_destroy", "pcnn_nn1_f32",
-    "pcnn_release_cached", "pcnn_debug_warp_times",
+    "pcnn_release_cached", "pcnn_debug_warp_times", "pcnn_iss_detect", "pcnn_iss_detect_host",
 ]
 
 
@@ -100,6 +105,8 @@ def lib():
     L.pcnn_nn1_f32.argtypes = [vp, vp, i64, i32, vp, vp, vp]
     L.pcnn_release_cached.argtypes = [i32]
     L.pcnn_debug_warp_times.argtypes = [vp, vp]
+    L.pcnn_iss_detect.argtypes = [vp, C.POINTER(IssParams), vp, i64, C.POINTER(i64), vp, vp]
+    L.pcnn_iss_detect_host.argtypes = [vp, C.POINTER(IssParams), vp, i64, C.POINTER(i64), vp]
     for name in EXPORTS:
         f = getattr(L, name)
         if name not in ("pcnn_last_error", "pcnn_icp_sums_dev"):

@@ -275,4 +275,55 @@ int pcnn_icp_host(const pcnn_index* target, const float* tar_normals_host, const
     return rc;
 }
 
+int pcnn_iss_detect(const pcnn_index* index, const pcnn_iss_params* params, int32_t* out_idx_dev,
+                    int64_t capacity, int64_t* out_count_host, float* out_lambda3_dev, pcnn_stream stream) {
+    PCNN_CHECK_ARG(index && params && out_count_host, "pcnn_iss_detect: NULL argument");
+    PCNN_CHECK_ARG(capacity >= 0 && (capacity == 0 || out_idx_dev), "pcnn_iss_detect: out_idx is NULL or capacity negative");
+    PCNN_CHECK_ARG(params->local_radius == params->local_radius && params->non_max_radius == params->non_max_radius,
+                   "pcnn_iss_detect: radius is NaN");
+    DeviceGuard g(index->device);
+    if (!g.ok) { set_error("pcnn_iss_detect: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
+    cudaStream_t s = (cudaStream_t)stream;
+    Scratch sc(s);
+    int64_t* count_dev;
+    PCNN_CUDA(sc.get(&count_dev, 1));
+    int rc = launch_iss(index, params, out_idx_dev, capacity, count_dev, out_lambda3_dev, s);
+    if (rc != PCNN_OK) return rc;
+    PCNN_CUDA(cudaMemcpyAsync(out_count_host, count_dev, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    PCNN_CUDA(cudaStreamSynchronize(s));
+    return PCNN_OK;
+}
+
+int pcnn_iss_detect_host(const pcnn_index* index, const pcnn_iss_params* params, int32_t* out_idx_host,
+                         int64_t capacity, int64_t* out_count_host, float* out_lambda3_host) {
+    PCNN_CHECK_ARG(index && params && out_count_host, "pcnn_iss_detect_host: NULL argument");
+    PCNN_CHECK_ARG(capacity >= 0 && (capacity == 0 || out_idx_host), "pcnn_iss_detect_host: out_idx is NULL or capacity negative");
+    DeviceGuard g(index->device);
+    if (!g.ok) { set_error("pcnn_iss_detect_host: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
+    cudaStream_t s = nullptr;
+    PCNN_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    int rc = PCNN_OK;
+    {
+        Scratch sc(s);
+        int32_t* idx_dev = nullptr;
+        float* lam_dev = nullptr;
+        const int64_t cap = capacity < index->n ? capacity : index->n;  // never more keypoints than points
+        cudaError_t e = sc.get(&idx_dev, (size_t)(cap > 0 ? cap : 1));
+        if (e == cudaSuccess && out_lambda3_host) e = sc.get(&lam_dev, (size_t)(index->n > 0 ? index->n : 1));
+        if (e != cudaSuccess) { set_error("pcnn_iss_detect_host: device allocation failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_NOMEM; }
+        if (rc == PCNN_OK) rc = pcnn_iss_detect(index, params, idx_dev, cap, out_count_host, lam_dev, (pcnn_stream)s);
+        if (rc == PCNN_OK) {
+            const int64_t got = *out_count_host < cap ? *out_count_host : cap;
+            if (got > 0 && cudaMemcpyAsync(out_idx_host, idx_dev, sizeof(int32_t) * (size_t)got, cudaMemcpyDeviceToHost, s) != cudaSuccess) rc = PCNN_ERR_CUDA;
+            if (rc == PCNN_OK && lam_dev && index->n > 0 &&
+                cudaMemcpyAsync(out_lambda3_host, lam_dev, sizeof(float) * (size_t)index->n, cudaMemcpyDeviceToHost, s) != cudaSuccess) rc = PCNN_ERR_CUDA;
+            if (cudaStreamSynchronize(s) != cudaSuccess) rc = PCNN_ERR_CUDA;
+            if (rc == PCNN_ERR_CUDA) set_error("pcnn_iss_detect_host: copy back failed: %s", cudaGetErrorString(cudaGetLastError()));
+        }
+    }
+    cudaStreamSynchronize(s);
+    cudaStreamDestroy(s);
+    return rc;
+}
+
 }  // extern "C"

@@ -151,6 +151,10 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq, int stride, int
                float* out_dist, double* out_dist64, cudaStream_t s);
 int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq, int stride, double radius,
                         int64_t* out_offsets, cudaStream_t s);
+// exclusive scan of nq int64 counts into offsets[nq + 1] (pcnn_radius.cu)
+int scan_counts(const long long* counts, int nq, long long* offsets, Scratch& sc, cudaStream_t s);
+int launch_iss(const pcnn_index* ix, const pcnn_iss_params* prm, int32_t* out_idx, int64_t capacity,
+               int64_t* out_count_dev, float* out_lambda3, cudaStream_t s);
 void note_radius_total(const pcnn_index* ix, const float* q, int64_t nq, double radius, int64_t total);
 int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq, int stride, double radius,
                        const int64_t* offsets, int32_t* out_idx, float* out_dist, double* out_dist64,

@@ -506,7 +506,7 @@ __global__ void __launch_bounds__(1024) scan_add_kernel(long long* __restrict__ 
     if (blockIdx.x == 0 && threadIdx.x == 0) offsets[nq] = tile_sums[ntiles];
 }
 
-static int scan_counts(const long long* counts, int nq, long long* offsets, Scratch& sc, cudaStream_t s) {
+int scan_counts(const long long* counts, int nq, long long* offsets, Scratch& sc, cudaStream_t s) {
     const int ntiles = (nq + SCAN_TILE - 1) / SCAN_TILE;
     long long* tile_sums;
     PCNN_CUDA(sc.get(&tile_sums, (size_t)ntiles + 1));

@@ -5,7 +5,7 @@ import ctypes as C
 import numpy as np
 
 from . import api
-from .api import (IcpParams, IcpResult, IndexInfo, KDTREE, OCTREE, _check, _dev_xyz, _host_xyz,
+from .api import (IcpParams, IcpResult, IndexInfo, IssParams, KDTREE, OCTREE, _check, _dev_xyz, _host_xyz,
                   _is_torch, _np_ptr, _stream, _t_ptr, lib)
 
 
@@ -152,6 +152,28 @@ class Index:
         if _is_torch(q):
             return idx, d2
         return idx.cpu().numpy(), d2.cpu().numpy()
+
+    # ------------------------------------------------------------------ ISS keypoints
+    def iss_keypoints(self, local_radius, non_max_radius, gamma21=0.9, gamma32=0.9, min_neighbors=5,
+                      weighted=True, device_out=False):
+        """ISS keypoints of the indexed cloud: ``ISSKeypoint::compute`` with the setters'
+        parameters (Homework7/hw7/src/iss_detector.cpp:38-111; defaults as main.cpp:95-101 uses
+        them).  Returns (keypoint indices ascending, lambda3[n] with -1 for non-candidates)."""
+        n = self.info()["n_points"]
+        prm = IssParams(local_radius, non_max_radius, gamma21, gamma32, min_neighbors, 1 if weighted else 0)
+        count = C.c_int64(0)
+        if device_out:
+            import torch
+            dev = torch.device("cuda", self.device)
+            idx = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+            lam = torch.empty(max(n, 1), dtype=torch.float32, device=dev)
+            _check(lib().pcnn_iss_detect(self._h, C.byref(prm), _t_ptr(idx), n, C.byref(count), _t_ptr(lam),
+                                         _stream()))
+            return idx[:count.value], lam[:n]
+        idx = np.empty(max(n, 1), np.int32)
+        lam = np.empty(max(n, 1), np.float32)
+        _check(lib().pcnn_iss_detect_host(self._h, C.byref(prm), _np_ptr(idx), n, C.byref(count), _np_ptr(lam)))
+        return idx[:count.value].copy(), lam[:n]
 
     # ------------------------------------------------------------------ ICP
     def icp(self, src, tar_normals=None, init_T=None, max_iter=30, max_corres_dist=1.0,

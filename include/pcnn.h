@@ -228,6 +228,40 @@ int pcnn_icp_destroy(pcnn_icp_state* st);
 int pcnn_nn1_f32(const pcnn_index* index, const float* q_dev, int64_t nq, int stride,
                  int32_t* out_idx_dev, float* out_d2_dev, pcnn_stream stream);
 
+/* ------------------------------------------------------------------ ISS keypoints
+ * (the reference's batched consumer of its own radius search.)
+ * Replaces ISSKeypoint::compute (Homework7/hw7/src/iss_detector.cpp:38-111) and
+ * getEigenvalues (:114-152) with the setters' parameters (iss_detector.hpp:18-24):
+ * neighbourhoods of every point of the indexed cloud at local_radius; scatter matrix about
+ * the point itself, neighbours weighted by 1/|their own neighbourhood| when `weighted`
+ * (useWeightedCovMat); eigenvalues l1 >= l2 >= l3; a point is a candidate when it has >= 3
+ * neighbours, l2/l1 < gamma21, l3/l2 < gamma32 and l3 > 0; a candidate is a keypoint when it
+ * has >= min_neighbors points within non_max_radius and none of them has a larger l3.
+ * Neighbourhoods follow Homework7's float KD-tree: key accumulated x, y, z with every step
+ * rounded to float, hit iff sqrtf(key) <= radius (kdtree.cpp:347-355, resultSet.hpp:127-136).
+ * The index may be of either kind; it must have been built over the cloud to analyse.
+ *   out_idx_dev     [capacity] keypoint indices (original point order), ascending, as the
+ *                   reference emits them (:104-105); entries beyond capacity are dropped
+ *   out_count       number of keypoints found (may exceed capacity)
+ *   out_lambda3_dev optional [n]: l3 of every candidate, -1 for the others (the reference's
+ *                   lambda3_vec_forall, :69)
+ * pcnn_iss_detect returns after ONE host synchronisation (the count); nothing is materialised
+ * per neighbour. */
+typedef struct {
+    float local_radius;
+    float non_max_radius;
+    float gamma21;
+    float gamma32;
+    int32_t min_neighbors;
+    int32_t weighted;
+} pcnn_iss_params;
+
+int pcnn_iss_detect(const pcnn_index* index, const pcnn_iss_params* params, int32_t* out_idx_dev,
+                    int64_t capacity, int64_t* out_count_host, float* out_lambda3_dev, pcnn_stream stream);
+/* Same with host outputs (out_lambda3_host may be NULL). */
+int pcnn_iss_detect_host(const pcnn_index* index, const pcnn_iss_params* params, int32_t* out_idx_host,
+                         int64_t capacity, int64_t* out_count_host, float* out_lambda3_host);
+
 #ifdef __cplusplus
 }
 #endif

@@ -104,6 +104,31 @@ class Oracle:
     def _fn(self, name):
         return getattr(self.nn, self.pfx + name)
 
+    # ---- ISS keypoints (port only: oracle/port_iss.cpp)
+    def iss(self, xyz, local_radius, non_max_radius, gamma21=0.9, gamma32=0.9, min_neighbors=5, weighted=True,
+            nthreads=8):
+        """(keypoint indices ascending, lambda3[n]) as ISSKeypoint::compute (iss_detector.cpp:38-111)."""
+        a = np.ascontiguousarray(_xyz(xyz)[:, :3])
+        n = a.shape[0]
+        lam = np.empty(max(n, 1), np.float32)
+        flag = np.zeros(max(n, 1), np.uint8)
+        f = self.nn.pco_iss
+        f.restype = C.c_int
+        f.argtypes = [_f32p, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, _f32p,
+                      C.POINTER(C.c_uint8), C.c_int]
+        f(_ptr(a, _f32p), n, local_radius, non_max_radius, gamma21, gamma32, min_neighbors, 1 if weighted else 0,
+          _ptr(lam, _f32p), flag.ctypes.data_as(C.POINTER(C.c_uint8)), nthreads)
+        return np.flatnonzero(flag[:n]).astype(np.int32), lam[:n]
+
+    def iss_counts(self, xyz, radius, nthreads=8):
+        a = np.ascontiguousarray(_xyz(xyz)[:, :3])
+        out = np.zeros(max(a.shape[0], 1), np.int32)
+        f = self.nn.pco_iss_counts
+        f.restype = C.c_int
+        f.argtypes = [_f32p, C.c_int64, C.c_float, _i32p, C.c_int]
+        f(_ptr(a, _f32p), a.shape[0], radius, _ptr(out, _i32p), nthreads)
+        return out[:a.shape[0]]
+
     def hardware_threads(self):
         return int(self._fn("hardware_threads")())
 
@@ -150,6 +175,22 @@ class Oracle:
         self.nn.pcport_brute_knn(_ptr(xyz, _f32p), xyz.shape[0], xyz.shape[1], _ptr(q, _f32p),
                                  q.shape[0], q.shape[1], k, _ptr(idx, _i32p), _ptr(d2, _f64p), nthreads)
         return idx, d2
+
+
+def ref_hw7_radius_all(xyz, radius):
+    """Neighbour lists of every point by the UNMODIFIED Homework7 float KD-tree
+    (oracle/_ref/libpcnn_ref_hw7.so, oracle/ref_iss_nn.cpp): CSR (offsets, idx in traversal order)."""
+    L = C.CDLL(os.path.join(_HERE, "_ref", "libpcnn_ref_hw7.so"))
+    f = L.ref7_radius_all
+    f.restype = C.c_int
+    f.argtypes = [_f32p, C.c_int64, C.c_float, _i64p, _i32p]
+    a = np.ascontiguousarray(_xyz(xyz)[:, :3])
+    n = a.shape[0]
+    off = np.zeros(n + 1, np.int64)
+    f(_ptr(a, _f32p), n, radius, _ptr(off, _i64p), None)
+    idx = np.empty(max(int(off[n]), 1), np.int32)
+    f(_ptr(a, _f32p), n, radius, _ptr(off, _i64p), _ptr(idx, _i32p))
+    return off, idx[:int(off[n])]
 
 
 class _Tree:

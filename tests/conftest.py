@@ -68,6 +68,11 @@ def golden_nn():
 
 
 @pytest.fixture(scope="session")
+def golden_iss():
+    return np.load(os.path.join(GOLDEN, "golden_iss.npz"))
+
+
+@pytest.fixture(scope="session")
 def golden_icp():
     return np.load(os.path.join(GOLDEN, "golden_icp.npz"))
 

@@ -35,6 +35,9 @@ WORKLOAD = ("kNN k=8, 1M-point synthetic KITTI-like aggregate (9 frames) x 1M qu
             "(second aggregate, path offset 1 m)")
 
 
+ISS_LOCAL_R, ISS_NMS_R = 0.5, 0.3  # metres, for the KITTI-like aggregate
+
+
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
@@ -212,6 +215,15 @@ def cpu_baseline(pts, qry):
             dt_i = time.perf_counter() - t
             out[name] = {"iters_per_s": r["iters"] / dt_i, "cores": cores, "kind": "port",
                          "sample": "restated loop (nanoflann 1-NN over %d threads), %d iterations incl. one kd-tree build" % (cores, r["iters"])}
+        # ISS keypoints: the restated detector on a 100k-point slice of the cloud
+        port = po.Oracle("port")
+        sub = np.ascontiguousarray(pts[:100_000, :3])
+        t = time.perf_counter()
+        kp, _ = port.iss(sub, ISS_LOCAL_R, ISS_NMS_R, 0.9, 0.9, 5, True, nthreads=cores)
+        dt_s = time.perf_counter() - t
+        out["iss_keypoints"] = {"points_per_s": len(sub) / dt_s, "cores": cores, "kind": "port",
+                                "sample": "oracle/port_iss.cpp (grid neighbourhoods) on the first 100k points, "
+                                          "%d keypoints" % len(kp)}
     except Exception as exc:  # a baseline leg must never sink the bench line
         out["extra_error"] = repr(exc)
     return out
@@ -238,7 +250,19 @@ def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):
                           "ms": ms, "algorithmic_GBps": alg / (ms * 1e-3) / 1e9,
                           "hbm_frac": alg / (ms * 1e-3) / 1e9 / peak, "passes": "count + scan + fill, all timed"}
     del off, idx, dist
-    # k = 32 (warp-per-query kernel), 200k queries
+    # ISS keypoints of the whole 1M cloud: three fused passes + compaction, one host sync
+    ix.iss_keypoints(ISS_LOCAL_R, ISS_NMS_R, device_out=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    kp, lam = ix.iss_keypoints(ISS_LOCAL_R, ISS_NMS_R, device_out=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    out["iss_keypoints_1M"] = {"points_per_s": N_POINTS / (ev0.elapsed_time(ev1) * 1e-3), "ms": ev0.elapsed_time(ev1),
+                               "keypoints": int(kp.shape[0]), "candidates": int((lam >= 0).sum().item()),
+                               "params": {"local_radius": ISS_LOCAL_R, "non_max_radius": ISS_NMS_R, "gamma21": 0.9,
+                                          "gamma32": 0.9, "min_neighbors": 5, "weighted": True}}
+    del kp, lam
+    # k = 32 (lock-step heap kernel), all 1M queries
     ix.knn(d_q[:1000], 32, dist="f32")
     torch.cuda.synchronize()
     ev0.record()

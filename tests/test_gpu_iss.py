@@ -127,3 +127,22 @@ def test_iss_edge_cases(oracle_port):
     rc = api.lib().pcnn_iss_detect_host(ix2._h, C.byref(bad), small.ctypes.data_as(C.c_void_p), 3, C.byref(count), None)
     assert rc == api.ERR_INVALID
     ix.close(); ix2.close()
+
+
+def test_iss_through_cpp_compat_class(golden_iss, tmp_path):
+    # the reference's calling code (main.cpp:81-103) against include/pcnn_iss_compat.hpp
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg = os.path.join(root, "hands-on-point-cloud-processing_b200")
+    exe = str(tmp_path / "iss_main")
+    subprocess.check_call(["g++", "-std=c++14", "-O2", "-Wall", "-Werror", "-I" + os.path.join(root, "include"),
+                           os.path.join(root, "tests", "compat", "iss_main.cpp"), "-o", exe,
+                           "-L" + pkg, "-lpcnn", "-Wl,-rpath," + pkg])
+    raw = str(tmp_path / "chair.f32")
+    golden_iss["pts"].tofile(raw)
+    out = subprocess.check_output([exe, raw, str(len(golden_iss["pts"]))]).decode().strip().split("\n")
+    kp = golden_iss["port_keypoints"]
+    assert out[0] == "key points size : %d" % len(kp)
+    got = np.array([[float(v) for v in ln.split()] for ln in out[1:]], np.float32)
+    assert np.array_equal(got, golden_iss["pts"][kp])

@@ -262,6 +262,21 @@ def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):
                                "params": {"local_radius": ISS_LOCAL_R, "non_max_radius": ISS_NMS_R, "gamma21": 0.9,
                                           "gamma32": 0.9, "min_neighbors": 5, "weighted": True}}
     del kp, lam
+    # voxel-grid downsample of the 1M cloud with normals, leaf 0.5 m (HBM-bound byte work)
+    d_p, d_n = torch.from_numpy(pts).to(dev), torch.from_numpy(nrm).to(dev)
+    pc.voxel_downsample(d_p, d_n, 0.5)
+    torch.cuda.synchronize()
+    ev0.record()
+    vx, vn = pc.voxel_downsample(d_p, d_n, 0.5)
+    ev1.record()
+    torch.cuda.synchronize()
+    vms = ev0.elapsed_time(ev1)
+    # algorithmic bytes: 24 B read per point for the means + 12 B for the keys, 24 B written per voxel
+    valg = 36 * N_POINTS + 24 * int(vx.shape[0])
+    out["voxel_grid_1M"] = {"points_per_s": N_POINTS / (vms * 1e-3), "ms": vms, "voxels": int(vx.shape[0]), "leaf": 0.5,
+                            "algorithmic_GBps": valg / (vms * 1e-3) / 1e9, "hbm_frac": valg / (vms * 1e-3) / 1e9 / peak,
+                            "timed": "whole call: bounding box + keys + radix sort + scan + means, two host syncs"}
+    del d_p, d_n, vx, vn
     # k = 32 (lock-step heap kernel), all 1M queries
     ix.knn(d_q[:1000], 32, dist="f32")
     torch.cuda.synchronize()

@@ -9,6 +9,7 @@ from .index import Index, IcpState  # noqa: F401
 from .compat import (DistIndex, KNNResultSet, RadiusNNResultSet, kdtree_construction,  # noqa: F401
                      kdtree_knn_search, kdtree_radius_search, octree_construction,
                      octree_knn_search, octree_radius_search, knn_search_batch,
-                     radius_search_batch, read_velodyne_bin)
+                     radius_search_batch, read_velodyne_bin, read_xyz_normal_bin, voxel_downsample,
+                     read_binary_and_voxel_down)
 from .sharding import shard_range, allreduce_icp_sums  # noqa: F401
 from . import synth  # noqa: F401

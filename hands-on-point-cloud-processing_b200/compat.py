@@ -169,3 +169,52 @@ def read_velodyne_bin(path, duplicate_last=False):
     if duplicate_last and len(pts):
         pts = np.concatenate([pts, pts[-1:]], axis=0)
     return np.ascontiguousarray(pts)
+
+
+# ------------------------------------------------------------------ cloud ingest + voxel grid
+def read_xyz_normal_bin(path, trailing_record=True):
+    """The 6-float (x, y, z, nx, ny, nz float32) record file of Homework9 -> (xyz [N,3], normals
+    [N,3]); the reader of readBinaryAndVoxelDown (Homework9/hw9/src/registration.cpp:12-29).
+    Its loop `for (; input.good() and !input.eof();)` runs once more after the last record, and
+    the read that fails leaves a default-constructed pcl::PointNormal (all zeros) in the cloud:
+    ``trailing_record=True`` reproduces that extra (0,0,0) point with a zero normal."""
+    raw = np.fromfile(path, dtype=np.float32)
+    raw = raw[: (len(raw) // 6) * 6].reshape(-1, 6)
+    if trailing_record:
+        raw = np.concatenate([raw, np.zeros((1, 6), np.float32)], axis=0)
+    return np.ascontiguousarray(raw[:, :3]), np.ascontiguousarray(raw[:, 3:])
+
+
+def voxel_downsample(xyz, normals=None, leaf=1.75, device=0):
+    """pcl::VoxelGrid<pcl::PointNormal> as the reference configures it (registration.cpp:37-41,
+    :688-691; leaf 1.75 is VoxelGridSampling's): one point per occupied voxel, ascending voxel
+    index.  numpy in -> numpy out, CUDA tensors in -> CUDA tensors out.  Returns (xyz, normals)."""
+    import ctypes as C
+    from . import api
+    from .api import _check, _is_torch, _np_ptr, _stream, _t_ptr, lib
+    lx, ly, lz = (leaf, leaf, leaf) if np.isscalar(leaf) else leaf
+    count = C.c_int64(0)
+    if _is_torch(xyz):
+        import torch
+        x = xyz.contiguous()
+        assert x.dtype == torch.float32 and x.dim() == 2 and x.shape[1] >= 3
+        nr = None if normals is None else normals.contiguous()
+        n = x.shape[0]
+        ox = torch.empty((max(n, 1), 3), dtype=torch.float32, device=x.device)
+        on = None if nr is None else torch.empty((max(n, 1), 3), dtype=torch.float32, device=x.device)
+        _check(lib().pcnn_voxel_downsample(_t_ptr(x), _t_ptr(nr), n, x.shape[1], 3 if nr is None else nr.shape[1],
+                                           lx, ly, lz, _t_ptr(ox), _t_ptr(on), n, C.byref(count), x.device.index,
+                                           _stream()))
+        return ox[:count.value], (None if on is None else on[:count.value])
+    import torch
+    dev = torch.device("cuda", device)
+    tx = torch.from_numpy(np.ascontiguousarray(xyz, np.float32)).to(dev)
+    tn = None if normals is None else torch.from_numpy(np.ascontiguousarray(normals, np.float32)).to(dev)
+    ox, on = voxel_downsample(tx, tn, (lx, ly, lz))
+    return ox.cpu().numpy(), (None if on is None else on.cpu().numpy())
+
+
+def read_binary_and_voxel_down(path, voxel_size, device=0):
+    """readBinaryAndVoxelDown(fileName, cloud, normals, voxel_size) (registration.cpp:8-68)."""
+    xyz, nrm = read_xyz_normal_bin(path)
+    return voxel_downsample(xyz, nrm, voxel_size, device)

@@ -262,6 +262,23 @@ int pcnn_iss_detect(const pcnn_index* index, const pcnn_iss_params* params, int3
 int pcnn_iss_detect_host(const pcnn_index* index, const pcnn_iss_params* params, int32_t* out_idx_host,
                          int64_t capacity, int64_t* out_count_host, float* out_lambda3_host);
 
+/* ------------------------------------------------------------------ voxel-grid downsample
+ *   Replaces the pcl::VoxelGrid<pcl::PointNormal> step of
+ * readBinaryAndVoxelDown (Homework9/hw9/src/registration.cpp:37-42: setDownsampleAllData(true),
+ * setLeafSize(v, v, v)) and Registration::VoxelGridSampling (:665-707, leaf 1.75), following
+ * PCL's published algorithm (pcl/filters/impl/voxel_grid.hpp, 1.8 - 1.10): one output point per
+ * occupied voxel in ascending voxel index (x fastest), position = mean of the voxel's points,
+ * normal = normalised sum of their normals; a grid with more than INT_MAX cells returns the
+ * input unchanged, as PCL does.  Means are formed in double and rounded once (PCL's float sums
+ * depend on the order std::sort leaves a voxel's points in).
+ *   xyz_dev [n*stride], normals_dev [n*normal_stride] or NULL; out_xyz_dev / out_normals_dev
+ *   [capacity*3] packed; out_count = number of occupied voxels (may exceed capacity; only the
+ *   first `capacity` are written).  Two host synchronisations (grid size, count). */
+int pcnn_voxel_downsample(const float* xyz_dev, const float* normals_dev, int64_t n, int stride,
+                          int normal_stride, float leaf_x, float leaf_y, float leaf_z,
+                          float* out_xyz_dev, float* out_normals_dev, int64_t capacity,
+                          int64_t* out_count_host, int device, pcnn_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -177,6 +177,59 @@ class Oracle:
         return idx, d2
 
 
+def voxel_grid(xyz, normals, leaf, sequential_float=False):
+    """CPU restatement of pcl::VoxelGrid<pcl::PointNormal>::applyFilter as the reference calls it
+    (Homework9/hw9/src/registration.cpp:37-41, :688-691), after PCL 1.8-1.10
+    pcl/filters/impl/voxel_grid.hpp and pcl/common/impl/accumulators.hpp (PCL is not vendored in
+    the reference and not installed here: PARITY UNPINNED, no golden vector exists).
+    Returns (xyz, normals, counts): one row per occupied voxel in ascending voxel index.
+    Means in float64 rounded once by default; ``sequential_float=True`` accumulates in float32 in
+    input order, which is what PCL does when std::sort happens to keep that order (small cases)."""
+    p = np.ascontiguousarray(xyz, np.float32)[:, :3]
+    n = len(p)
+    leaf = np.broadcast_to(np.asarray(leaf, np.float32), (3,))
+    inv = (np.float32(1.0) / leaf).astype(np.float32)
+    if n == 0:
+        return p.copy(), (None if normals is None else np.zeros((0, 3), np.float32)), np.zeros(0, np.int64)
+    lo, hi = p.min(0), p.max(0)
+    d = ((hi - lo) * inv).astype(np.int64) + 1
+    min_b = np.floor(lo * inv).astype(np.int64)
+    max_b = np.floor(hi * inv).astype(np.int64)
+    div = max_b - min_b + 1
+    if int(d[0]) * int(d[1]) * int(d[2]) > 2**31 - 1 or int(div[0]) * int(div[1]) * int(div[2]) > 2**31 - 1:
+        return p.copy(), (None if normals is None else np.ascontiguousarray(normals, np.float32)[:, :3].copy()), np.ones(n, np.int64)
+    ijk = (np.floor(p * inv) - min_b.astype(np.float32)).astype(np.int64)   # float32 arithmetic, then the int cast
+    idx = ijk[:, 0] + ijk[:, 1] * div[0] + ijk[:, 2] * div[0] * div[1]
+    order = np.argsort(idx, kind="stable")
+    sidx = idx[order]
+    heads = np.flatnonzero(np.append(True, sidx[1:] != sidx[:-1]))
+    counts = np.diff(np.append(heads, n))
+    nr = None if normals is None else np.ascontiguousarray(normals, np.float32)[:, :3]
+    if sequential_float:
+        ox = np.zeros((len(heads), 3), np.float32)
+        on = None if nr is None else np.zeros((len(heads), 3), np.float32)
+        for v, (b, c) in enumerate(zip(heads, counts)):
+            acc = np.zeros(3, np.float32)
+            accn = np.zeros(3, np.float32)
+            for i in order[b:b + c]:
+                acc = (acc + p[i]).astype(np.float32)
+                if nr is not None:
+                    accn = (accn + nr[i]).astype(np.float32)
+            ox[v] = acc / np.float32(c)
+            if nr is not None:
+                with np.errstate(invalid="ignore", divide="ignore"):
+                    on[v] = accn / np.sqrt((accn * accn).sum(dtype=np.float32))
+        return ox, on, counts
+    s = np.add.reduceat(p[order].astype(np.float64), heads, axis=0)
+    ox = (s / counts[:, None]).astype(np.float32)
+    on = None
+    if nr is not None:
+        sn = np.add.reduceat(nr[order].astype(np.float64), heads, axis=0)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            on = (sn / np.sqrt((sn * sn).sum(1))[:, None]).astype(np.float32)
+    return ox, on, counts
+
+
 def ref_hw7_radius_all(xyz, radius):
     """Neighbour lists of every point by the UNMODIFIED Homework7 float KD-tree
     (oracle/_ref/libpcnn_ref_hw7.so, oracle/ref_iss_nn.cpp): CSR (offsets, idx in traversal order)."""

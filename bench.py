@@ -262,6 +262,18 @@ def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):
                                "params": {"local_radius": ISS_LOCAL_R, "non_max_radius": ISS_NMS_R, "gamma21": 0.9,
                                           "gamma32": 0.9, "min_neighbors": 5, "weighted": True}}
     del kp, lam
+    # normals by PCA over the 10 nearest neighbours within 1 m, all 1M points (pca_normal.py:93's loop)
+    ix.estimate_normals(10, 1.0, device_out=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    nn_ = ix.estimate_normals(10, 1.0, device_out=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    out["pca_normals_1M"] = {"points_per_s": N_POINTS / (ev0.elapsed_time(ev1) * 1e-3), "ms": ev0.elapsed_time(ev1),
+                             "max_nn": 10, "radius": 1.0,
+                             "median_abs_dot_with_generator_normals": float(
+                                 (nn_ * torch.from_numpy(nrm).to(dev)).sum(1).abs().median().item())}
+    del nn_
     # voxel-grid downsample of the 1M cloud with normals, leaf 0.5 m (HBM-bound byte work)
     d_p, d_n = torch.from_numpy(pts).to(dev), torch.from_numpy(nrm).to(dev)
     pc.voxel_downsample(d_p, d_n, 0.5)

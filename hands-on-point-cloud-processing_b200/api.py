@@ -65,7 +65,7 @@ EXPORTS = [
     "pcnn_radius_host", "pcnn_icp", "pcnn_icp_host", "pcnn_icp_create", "pcnn_icp_accumulate",
     "pcnn_icp_sums_dev", "pcnn_icp_update", "pcnn_icp_finish", "pcnn_icp_destroy", "pcnn_nn1_f32",
     "pcnn_release_cached", "pcnn_debug_warp_times", "pcnn_iss_detect", "pcnn_iss_detect_host",
-    "pcnn_voxel_downsample",
+    "pcnn_voxel_downsample", "pcnn_estimate_normals", "pcnn_estimate_normals_host",
 ]
 
 
@@ -108,6 +108,8 @@ def lib():
     L.pcnn_debug_warp_times.argtypes = [vp, vp]
     L.pcnn_iss_detect.argtypes = [vp, C.POINTER(IssParams), vp, i64, C.POINTER(i64), vp, vp]
     L.pcnn_iss_detect_host.argtypes = [vp, C.POINTER(IssParams), vp, i64, C.POINTER(i64), vp]
+    L.pcnn_estimate_normals.argtypes = [vp, i32, f64, vp, vp]
+    L.pcnn_estimate_normals_host.argtypes = [vp, i32, f64, vp]
     L.pcnn_voxel_downsample.argtypes = [vp, vp, i64, i32, i32, f32, f32, f32, vp, vp, i64, C.POINTER(i64), i32, vp]
     for name in EXPORTS:
         f = getattr(L, name)

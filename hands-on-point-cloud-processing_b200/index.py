@@ -153,6 +153,20 @@ class Index:
             return idx, d2
         return idx.cpu().numpy(), d2.cpu().numpy()
 
+    # ------------------------------------------------------------------ normals by PCA over kNN
+    def estimate_normals(self, max_nn=10, radius=5.0, device_out=False):
+        """Normals of the indexed cloud: the per-point loop of pca_normal.py:85-101 (hybrid search
+        radius=5, max_nn=10 there).  [n, 3] float32, original point order, sign arbitrary."""
+        n = self.info()["n_points"]
+        if device_out:
+            import torch
+            out = torch.empty((n, 3), dtype=torch.float32, device=torch.device("cuda", self.device))
+            _check(lib().pcnn_estimate_normals(self._h, max_nn, float(radius), _t_ptr(out), _stream()))
+            return out
+        out = np.empty((n, 3), np.float32)
+        _check(lib().pcnn_estimate_normals_host(self._h, max_nn, float(radius), _np_ptr(out)))
+        return out
+
     # ------------------------------------------------------------------ ISS keypoints
     def iss_keypoints(self, local_radius, non_max_radius, gamma21=0.9, gamma32=0.9, min_neighbors=5,
                       weighted=True, device_out=False):

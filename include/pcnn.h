@@ -279,6 +279,19 @@ int pcnn_voxel_downsample(const float* xyz_dev, const float* normals_dev, int64_
                           float* out_xyz_dev, float* out_normals_dev, int64_t capacity,
                           int64_t* out_count_host, int device, pcnn_stream stream);
 
+/* ------------------------------------------------------------------ normals by PCA over kNN
+ *   Replaces the per-point loop of the reference's normal estimation
+ * (Homework1/YuF_KIT-.../pca_normal.py:85-101 with PCA(), :17-33): for every point of the
+ * indexed cloud the at most max_nn nearest neighbours within `radius` (the point itself
+ * included; open3d search_hybrid_vector_3d(radius, max_nn), :93); with >= 3 of them the normal
+ * is the eigenvector of the smallest eigenvalue of sum (p - mean)(p - mean)^T, unit length;
+ * otherwise (0, 0, 0).  out_normals [n*3] packed, original point order.  The sign of a normal
+ * is arbitrary, as it is in the reference (LAPACK's): compare up to sign.
+ * 1 <= max_nn <= PCNN_MAX_K. */
+int pcnn_estimate_normals(const pcnn_index* index, int max_nn, double radius, float* out_normals_dev,
+                          pcnn_stream stream);
+int pcnn_estimate_normals_host(const pcnn_index* index, int max_nn, double radius, float* out_normals_host);
+
 #ifdef __cplusplus
 }
 #endif

@@ -177,6 +177,33 @@ class Oracle:
         return idx, d2
 
 
+def pca_normals(xyz, max_nn=10, radius=5.0, oracle=None, nthreads=8):
+    """CPU restatement of the reference's normal estimation loop
+    (Homework1/YuF_KIT-.../pca_normal.py:85-101, PCA() :17-33): hybrid search (<= max_nn nearest
+    within radius, the point itself included), PCA of the found points, eigenvector of the
+    smallest eigenvalue; zero when fewer than 3 are found.  The neighbour search is this oracle's
+    exact brute-force kNN (open3d is not installed here: PARITY UNPINNED); the PCA is numpy's
+    eigh on the double scatter matrix (the reference calls np.linalg.eig on the same matrix).
+    Returns (normals [n,3] float64, eigenvalues [n,3] ascending) -- sign of a normal arbitrary."""
+    orc = oracle or Oracle("port")
+    p = np.ascontiguousarray(xyz, np.float32)[:, :3]
+    n = len(p)
+    k = min(max_nn, n)
+    idx, d2 = orc.brute_knn(p, p, k, nthreads=nthreads)
+    dist = np.sqrt(d2)
+    ok = (idx >= 0) & (dist <= radius)
+    m = ok.sum(1)
+    P = p.astype(np.float64)[np.where(ok, idx, 0)]                     # [n, k, 3]
+    w = ok[:, :, None].astype(np.float64)
+    c = (P * w).sum(1) / np.maximum(m, 1)[:, None]                      # :18
+    D = (P - c[:, None, :]) * w                                          # :19
+    XTX = np.einsum("nki,nkj->nij", D, D)                                # :20
+    ev, evec = np.linalg.eigh(XTX)                                       # ascending
+    normals = evec[:, :, 0].copy()
+    normals[m < 3] = 0.0                                                 # :94
+    return normals, ev
+
+
 def voxel_grid(xyz, normals, leaf, sequential_float=False):
     """CPU restatement of pcl::VoxelGrid<pcl::PointNormal>::applyFilter as the reference calls it
     (Homework9/hw9/src/registration.cpp:37-41, :688-691), after PCL 1.8-1.10

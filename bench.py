@@ -224,6 +224,17 @@ def cpu_baseline(pts, qry):
         out["iss_keypoints"] = {"points_per_s": len(sub) / dt_s, "cores": cores, "kind": "port",
                                 "sample": "oracle/port_iss.cpp (grid neighbourhoods) on the first 100k points, "
                                           "%d keypoints" % len(kp)}
+        rng = np.random.default_rng(5)
+        ks = rng.uniform(-10, 10, (3000, 3)).astype(np.float32)
+        kt = (ks @ pc_synth().rot_zx(25.0, 7.0).astype(np.float32).T + np.float32(1.0)).astype(np.float32)
+        kp = np.stack([np.arange(3000), np.arange(3000)], 1).astype(np.int32)
+        bad = rng.random(3000) < 0.7
+        kp[bad, 1] = rng.integers(0, 3000, bad.sum())
+        t = time.perf_counter()
+        port.ransac(ks, kt, kp, 8000, 0.1, 0.15, 1, nthreads=cores)
+        dt_k = time.perf_counter() - t
+        out["ransac_hyp_3k_pairs"] = {"hypotheses_per_s": 8000 / dt_k, "cores": cores, "kind": "port",
+                                      "sample": "oracle/port_ransac.cpp, 8,000 of the 80,000 hypotheses over 3,000 correspondences"}
     except Exception as exc:  # a baseline leg must never sink the bench line
         out["extra_error"] = repr(exc)
     return out
@@ -262,6 +273,32 @@ def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):
                                "params": {"local_radius": ISS_LOCAL_R, "non_max_radius": ISS_NMS_R, "gamma21": 0.9,
                                           "gamma32": 0.9, "min_neighbors": 5, "weighted": True}}
     del kp, lam
+    # global initialisation: 33-D mutual matching of 5k x 5k descriptors, then the reference's 80,000
+    # RANSAC hypotheses (main.cpp:86) over 3,000 correspondences with 70 % outliers
+    rng = np.random.default_rng(5)
+    sd = torch.from_numpy((rng.random((5000, 33)) * 100).astype(np.float32)).to(dev)
+    td = sd[torch.randperm(5000, device=dev)] + 0.5 * torch.randn((5000, 33), device=dev)
+    pc.match_descriptors(sd, td, "inter", 0.2)
+    torch.cuda.synchronize()
+    ev0.record()
+    mm = pc.match_descriptors(sd, td, "inter", 0.2)
+    ev1.record()
+    torch.cuda.synchronize()
+    out["match_5k_x_5k_33d"] = {"ms": ev0.elapsed_time(ev1), "pairs": int(mm.shape[0])}
+    ks = rng.uniform(-10, 10, (3000, 3)).astype(np.float32)
+    Rk = pc.synth.rot_zx(25.0, 7.0).astype(np.float32)
+    kt = (ks @ Rk.T + np.array([1.5, -2.0, 0.7], np.float32) + rng.normal(0, 0.01, (3000, 3))).astype(np.float32)
+    kp = np.stack([np.arange(3000), np.arange(3000)], 1).astype(np.int32)
+    bad = rng.random(3000) < 0.7
+    kp[bad, 1] = rng.integers(0, 3000, bad.sum())
+    d_ks, d_kt, d_kp = torch.from_numpy(ks).to(dev), torch.from_numpy(kt).to(dev), torch.from_numpy(kp).to(dev)
+    pc.ransac(d_ks, d_kt, d_kp, 80000, 0.1, seed=1)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    rr = pc.ransac(d_ks, d_kt, d_kp, 80000, 0.1, seed=1)
+    dt = time.perf_counter() - t0
+    out["ransac_80k_hyp_3k_pairs"] = {"ms": 1e3 * dt, "hypotheses_per_s": 80000 / dt, "consensus": rr["consensus"],
+                                      "rot_err_vs_truth": float(np.abs(rr["R"] - Rk).max())}
     # normals by PCA over the 10 nearest neighbours within 1 m, all 1M points (pca_normal.py:93's loop)
     ix.estimate_normals(10, 1.0, device_out=True)
     torch.cuda.synchronize()

@@ -10,6 +10,6 @@ from .compat import (DistIndex, KNNResultSet, RadiusNNResultSet, kdtree_construc
                      kdtree_knn_search, kdtree_radius_search, octree_construction,
                      octree_knn_search, octree_radius_search, knn_search_batch,
                      radius_search_batch, read_velodyne_bin, read_xyz_normal_bin, voxel_downsample,
-                     read_binary_and_voxel_down)
+                     read_binary_and_voxel_down, desc_nn1, match_descriptors, ransac)
 from .sharding import shard_range, allreduce_icp_sums  # noqa: F401
 from . import synth  # noqa: F401

@@ -58,6 +58,15 @@ class IssParams(C.Structure):
                 ("gamma32", C.c_float), ("min_neighbors", C.c_int32), ("weighted", C.c_int32)]
 
 
+class RansacParams(C.Structure):
+    _fields_ = [("max_iter", C.c_int32), ("dist_threshold", C.c_float), ("coplanar_min", C.c_float),
+                ("reserved", C.c_int32), ("seed", C.c_uint64)]
+
+
+class RansacResult(C.Structure):
+    _fields_ = [("R", C.c_float * 9), ("t", C.c_float * 3), ("consensus", C.c_int64), ("best_iter", C.c_int64)]
+
+
 EXPORTS = [
     "pcnn_last_error", "pcnn_version", "pcnn_device_count", "pcnn_index_build",
     "pcnn_index_build_host", "pcnn_index_destroy", "pcnn_index_get_info", "pcnn_knn",
@@ -66,6 +75,7 @@ EXPORTS = [
     "pcnn_icp_sums_dev", "pcnn_icp_update", "pcnn_icp_finish", "pcnn_icp_destroy", "pcnn_nn1_f32",
     "pcnn_release_cached", "pcnn_debug_warp_times", "pcnn_iss_detect", "pcnn_iss_detect_host",
     "pcnn_voxel_downsample", "pcnn_estimate_normals", "pcnn_estimate_normals_host",
+    "pcnn_desc_nn1", "pcnn_match_descriptors", "pcnn_ransac",
 ]
 
 
@@ -110,6 +120,9 @@ def lib():
     L.pcnn_iss_detect_host.argtypes = [vp, C.POINTER(IssParams), vp, i64, C.POINTER(i64), vp]
     L.pcnn_estimate_normals.argtypes = [vp, i32, f64, vp, vp]
     L.pcnn_estimate_normals_host.argtypes = [vp, i32, f64, vp]
+    L.pcnn_desc_nn1.argtypes = [vp, i64, vp, i64, i32, vp, vp, i32, vp]
+    L.pcnn_match_descriptors.argtypes = [vp, i64, vp, i64, i32, i32, f32, vp, i64, C.POINTER(i64), i32, vp]
+    L.pcnn_ransac.argtypes = [vp, vp, vp, i64, C.POINTER(RansacParams), C.POINTER(RansacResult), i32, vp]
     L.pcnn_voxel_downsample.argtypes = [vp, vp, i64, i32, i32, f32, f32, f32, vp, vp, i64, C.POINTER(i64), i32, vp]
     for name in EXPORTS:
         f = getattr(L, name)

@@ -218,3 +218,56 @@ def read_binary_and_voxel_down(path, voxel_size, device=0):
     """readBinaryAndVoxelDown(fileName, cloud, normals, voxel_size) (registration.cpp:8-68)."""
     xyz, nrm = read_xyz_normal_bin(path)
     return voxel_downsample(xyz, nrm, voxel_size, device)
+
+
+# ------------------------------------------------------------------ global initialisation (SURVEY 8f rank 4)
+def _cuda(a, dtype, device):
+    import torch
+    if isinstance(a, torch.Tensor):
+        return a.to(dtype=dtype).contiguous()
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dtype=dtype, device=torch.device("cuda", device)).contiguous()
+
+
+def desc_nn1(a, b, device=0):
+    """Exact float32 1-NN of every row of ``a`` among the rows of ``b`` with nanoflann's arithmetic
+    (registration.cpp:458-492).  Returns CUDA tensors (idx int32 [na], d2 float32 [na])."""
+    import torch
+    from .api import _check, _stream, _t_ptr, lib
+    ta, tb = _cuda(a, torch.float32, device), _cuda(b, torch.float32, device)
+    idx = torch.empty(max(len(ta), 1), dtype=torch.int32, device=ta.device)
+    d2 = torch.empty(max(len(ta), 1), dtype=torch.float32, device=ta.device)
+    _check(lib().pcnn_desc_nn1(_t_ptr(ta), len(ta), _t_ptr(tb), len(tb), ta.shape[1], _t_ptr(idx), _t_ptr(d2),
+                               ta.device.index, _stream()))
+    return idx[:len(ta)], d2[:len(ta)]
+
+
+def match_descriptors(src_desc, tar_desc, mode="inter", rejection_rate=0.0, device=0):
+    """findRANSACCorrespondencesInter / ...Union (registration.cpp:437-527 / :530-611):
+    [(source index, target index)] int32 CUDA tensor, ascending descriptor distance."""
+    import ctypes as C
+    import torch
+    from .api import _check, _stream, _t_ptr, lib
+    ts, tt = _cuda(src_desc, torch.float32, device), _cuda(tar_desc, torch.float32, device)
+    cap = len(ts) + len(tt)
+    out = torch.empty((max(cap, 1), 2), dtype=torch.int32, device=ts.device)
+    count = C.c_int64(0)
+    _check(lib().pcnn_match_descriptors(_t_ptr(ts), len(ts), _t_ptr(tt), len(tt), ts.shape[1] if ts.dim() == 2 else 0,
+                                        {"inter": 0, "union": 1}[mode], float(rejection_rate), _t_ptr(out), cap,
+                                        C.byref(count), ts.device.index, _stream()))
+    return out[:count.value]
+
+
+def ransac(src_keypoints, tar_keypoints, pairs, max_iter=80000, dist_threshold=0.5, coplanar_min=0.15, seed=0, device=0):
+    """Registration::RANSAC (registration.cpp:288-434).  Returns a dict (R [3,3], t [3], consensus, best_iter)."""
+    import ctypes as C
+    import torch
+    from . import api
+    from .api import _check, _stream, _t_ptr, lib
+    s = _cuda(src_keypoints, torch.float32, device)[:, :3].contiguous()
+    t = _cuda(tar_keypoints, torch.float32, device)[:, :3].contiguous()
+    p = _cuda(pairs, torch.int32, device)
+    prm = api.RansacParams(max_iter, dist_threshold, coplanar_min, 0, seed)
+    res = api.RansacResult()
+    _check(lib().pcnn_ransac(_t_ptr(s), _t_ptr(t), _t_ptr(p), len(p), C.byref(prm), C.byref(res), s.device.index, _stream()))
+    return {"R": np.array(list(res.R), np.float32).reshape(3, 3), "t": np.array(list(res.t), np.float32),
+            "consensus": int(res.consensus), "best_iter": int(res.best_iter)}

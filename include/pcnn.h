@@ -292,6 +292,49 @@ int pcnn_estimate_normals(const pcnn_index* index, int max_nn, double radius, fl
                           pcnn_stream stream);
 int pcnn_estimate_normals_host(const pcnn_index* index, int max_nn, double radius, float* out_normals_host);
 
+/* ------------------------------------------------------------------ global initialisation
+ *   Descriptor matching and RANSAC before ICP, Homework9/hw9/src/registration.cpp.
+ *
+ * pcnn_desc_nn1: exact 1-NN of every row of a [na, dim] among the rows of b [nb, dim] in float32
+ * squared L2 with nanoflann's arithmetic (`result += diff * diff`, dimension by dimension), as the
+ * KDTreeEigenMatrixAdaptor searches of :458-492 return it; lowest index wins an exact tie.
+ * dim <= 64 (FPFHSignature33: 33).  out_idx [na] (-1 when nb == 0), out_d2 [na].
+ *
+ * pcnn_match_descriptors: mode 0 = findRANSACCorrespondencesInter (:437-527: pairs that are each
+ * other's nearest neighbour), mode 1 = findRANSACCorrespondencesUnion (:530-611: every target's
+ * and every source's pair); pairs sorted by ascending descriptor distance and the worst
+ * rejection_rate of them dropped, N = floor((1 - rate) * count) in float as at :516 / :603.
+ * out_pairs [capacity*2] = (source index, target index); out_count = N (may exceed capacity).
+ *
+ * pcnn_ransac: Registration::RANSAC (:288-434).  Hypothesis `it` (0 <= it < max_iter) samples 4
+ * distinct correspondences with a counter-based generator keyed by (seed, it) -- the reference
+ * seeds mt19937 from std::random_device and is not reproducible -- re-draws while the signed
+ * distance of the 4th source point from the plane of the first three is <= coplanar_min (0.15 at
+ * :358), solves R, t by the SVD of target * source^T with the reference's det < 0 branch, and
+ * counts the correspondences with |target - (R source + t)| <= dist_threshold.  Result: the
+ * hypothesis with the largest consensus, the earliest such iteration (the strict `>` of :423).
+ * All hypotheses are evaluated concurrently.  src/tar_kp_dev: packed xyz of the keypoints. */
+int pcnn_desc_nn1(const float* a_dev, int64_t na, const float* b_dev, int64_t nb, int dim,
+                  int32_t* out_idx_dev, float* out_d2_dev, int device, pcnn_stream stream);
+int pcnn_match_descriptors(const float* src_desc_dev, int64_t n_src, const float* tar_desc_dev, int64_t n_tar,
+                           int dim, int mode, float rejection_rate, int32_t* out_pairs_dev, int64_t capacity,
+                           int64_t* out_count_host, int device, pcnn_stream stream);
+typedef struct {
+    int32_t max_iter;       /* m_RANSAC_max_iter (80000 in main.cpp:86) */
+    float dist_threshold;   /* m_RANSAC_dist_threshold */
+    float coplanar_min;     /* 0.15 in the reference */
+    int32_t reserved;
+    uint64_t seed;
+} pcnn_ransac_params;
+typedef struct {
+    float R[9];             /* row-major */
+    float t[3];
+    int64_t consensus;      /* max_consensus_set_size; 0 = no hypothesis had an inlier */
+    int64_t best_iter;      /* the iteration that produced it, -1 if none */
+} pcnn_ransac_result;
+int pcnn_ransac(const float* src_kp_dev, const float* tar_kp_dev, const int32_t* pairs_dev, int64_t n_pairs,
+                const pcnn_ransac_params* params, pcnn_ransac_result* out_host, int device, pcnn_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -120,6 +120,37 @@ class Oracle:
           _ptr(lam, _f32p), flag.ctypes.data_as(C.POINTER(C.c_uint8)), nthreads)
         return np.flatnonzero(flag[:n]).astype(np.int32), lam[:n]
 
+    # ---- descriptor matching + RANSAC (port only: oracle/port_ransac.cpp)
+    def desc_nn1(self, a, b, nthreads=8):
+        a = np.ascontiguousarray(a, np.float32); b = np.ascontiguousarray(b, np.float32)
+        idx = np.full(max(len(a), 1), -1, np.int32); d2 = np.zeros(max(len(a), 1), np.float32)
+        f = self.nn.pco_desc_nn1
+        f.restype = C.c_int
+        f.argtypes = [_f32p, C.c_int64, _f32p, C.c_int64, C.c_int, _i32p, _f32p, C.c_int]
+        f(_ptr(a, _f32p), len(a), _ptr(b, _f32p), len(b), a.shape[1], _ptr(idx, _i32p), _ptr(d2, _f32p), nthreads)
+        return idx[:len(a)], d2[:len(a)]
+
+    def match(self, src_desc, tar_desc, mode=0, rejection_rate=0.0, nthreads=8):
+        sd = np.ascontiguousarray(src_desc, np.float32); td = np.ascontiguousarray(tar_desc, np.float32)
+        out = np.zeros((max(len(sd) + len(td), 1), 2), np.int32)
+        f = self.nn.pco_match
+        f.restype = C.c_int64
+        f.argtypes = [_f32p, C.c_int64, _f32p, C.c_int64, C.c_int, C.c_int, C.c_float, _i32p, C.c_int]
+        n = f(_ptr(sd, _f32p), len(sd), _ptr(td, _f32p), len(td), sd.shape[1], mode, rejection_rate, _ptr(out, _i32p), nthreads)
+        return out[:n].copy()
+
+    def ransac(self, src_kp, tar_kp, pairs, max_iter, dist_threshold, coplanar_min=0.15, seed=0, nthreads=8):
+        s = np.ascontiguousarray(src_kp, np.float32)[:, :3].copy(); t = np.ascontiguousarray(tar_kp, np.float32)[:, :3].copy()
+        p = np.ascontiguousarray(pairs, np.int32)
+        R = np.zeros(9, np.float32); tt = np.zeros(3, np.float32); it = C.c_int64(-1)
+        f = self.nn.pco_ransac
+        f.restype = C.c_int64
+        f.argtypes = [_f32p, _f32p, _i32p, C.c_int64, C.c_int, C.c_float, C.c_float, C.c_uint64, _f32p, _f32p,
+                      C.POINTER(C.c_int64), C.c_int]
+        cons = f(_ptr(s, _f32p), _ptr(t, _f32p), _ptr(p, _i32p), len(p), max_iter, dist_threshold, coplanar_min, seed,
+                 _ptr(R, _f32p), _ptr(tt, _f32p), C.byref(it), nthreads)
+        return {"R": R.reshape(3, 3), "t": tt, "consensus": int(cons), "best_iter": int(it.value)}
+
     def iss_counts(self, xyz, radius, nthreads=8):
         a = np.ascontiguousarray(_xyz(xyz)[:, :3])
         out = np.zeros(max(a.shape[0], 1), np.int32)

@@ -28,27 +28,35 @@ namespace pcnn {
 constexpr int DM_MAXDIM = 64;
 constexpr int DM_TILE = 64;  // candidates per shared-memory stage
 
-// nearest b for every a: out_idx[na], out_d2[na]
+// nearest b for every a.  grid.x tiles the queries (one per thread), grid.y slices the candidates
+// so that a few thousand queries still fill the machine; each slice folds its best into
+// packed[i] = (float bits of d2) << 32 | index by a 64-bit atomicMin: d2 >= 0, so the bit
+// patterns order like the values, and among equal distances the lowest index wins -- the same
+// answer as one sequential scan with a strict `<`.  D = compile-time dimension (0: any <= 64).
+template <int D>
 __global__ void __launch_bounds__(128) desc_nn1_kernel(const float* __restrict__ a, int na, const float* __restrict__ b,
-                                                       int nb, int dim, int32_t* __restrict__ out_idx,
-                                                       float* __restrict__ out_d2) {
-    __shared__ float sb[DM_TILE][DM_MAXDIM + 1];
+                                                       int nb, int dim_rt, int slice,
+                                                       unsigned long long* __restrict__ packed) {
+    constexpr int CAP = D > 0 ? D : DM_MAXDIM;
+    __shared__ float sb[DM_TILE][CAP + 1];
+    const int dim = D > 0 ? D : dim_rt;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    float q[DM_MAXDIM];
+    float q[CAP];
 #pragma unroll
-    for (int d = 0; d < DM_MAXDIM; d++) q[d] = (i < na && d < dim) ? a[(size_t)i * dim + d] : 0.f;
+    for (int d = 0; d < CAP; d++) q[d] = (i < na && d < dim) ? a[(size_t)i * dim + d] : 0.f;
     float best = __int_as_float(0x7f800000);
     int best_j = -1;
-    for (int j0 = 0; j0 < nb; j0 += DM_TILE) {
-        const int cnt = min(DM_TILE, nb - j0);
+    const int jbeg = blockIdx.y * slice, jend = min(nb, jbeg + slice);
+    for (int j0 = jbeg; j0 < jend; j0 += DM_TILE) {
+        const int cnt = min(DM_TILE, jend - j0);
         __syncthreads();
         for (int e = threadIdx.x; e < cnt * dim; e += blockDim.x) sb[e / dim][e % dim] = b[(size_t)j0 * dim + e];
         __syncthreads();
         for (int j = 0; j < cnt; j++) {
             float r = 0.f;
 #pragma unroll
-            for (int d = 0; d < DM_MAXDIM; d++) {
-                if (d < dim) {
+            for (int d = 0; d < CAP; d++) {
+                if (D > 0 || d < dim) {
                     const float diff = __fsub_rn(q[d], sb[j][d]);  // a[i] - data(b_idx, i)
                     r = __fadd_rn(r, __fmul_rn(diff, diff));       // result += diff * diff
                 }
@@ -56,7 +64,18 @@ __global__ void __launch_bounds__(128) desc_nn1_kernel(const float* __restrict__
             if (r < best) { best = r; best_j = j0 + j; }  // strict: the first (lowest index) wins a tie
         }
     }
-    if (i < na) { out_idx[i] = best_j; out_d2[i] = best; }
+    if (i < na && best_j >= 0)
+        atomicMin(packed + i, ((unsigned long long)__float_as_uint(best) << 32) | (unsigned)best_j);
+}
+
+__global__ void desc_unpack_kernel(const unsigned long long* __restrict__ packed, int na, int32_t* __restrict__ out_idx,
+                                   float* __restrict__ out_d2) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= na) return;
+    const unsigned long long p = packed[i];
+    const bool none = p == ~0ull;
+    out_idx[i] = none ? -1 : (int32_t)(p & 0xffffffffull);
+    out_d2[i] = none ? __int_as_float(0x7f800000) : __uint_as_float((unsigned)(p >> 32));
 }
 
 // Inter: pair (i, s2t[i]) kept when t2s[s2t[i]] == i.  Union: every target's and every source's pair.
@@ -244,8 +263,27 @@ extern "C" int pcnn_desc_nn1(const float* a_dev, int64_t na, const float* b_dev,
     DeviceGuard g(device);
     if (!g.ok) { set_error("pcnn_desc_nn1: cannot select CUDA device %d (no CPU fallback exists)", device); return PCNN_ERR_CUDA; }
     if (na == 0) return PCNN_OK;
-    desc_nn1_kernel<<<(unsigned)((na + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a_dev, (int)na, b_dev, (int)nb, dim,
-                                                                                    out_idx_dev, out_d2_dev);
+    cudaStream_t s = (cudaStream_t)stream;
+    Scratch sc(s);
+    unsigned long long* packed;
+    PCNN_CUDA(sc.get(&packed, (size_t)na));
+    PCNN_CUDA(cudaMemsetAsync(packed, 0xff, sizeof(unsigned long long) * (size_t)na, s));
+    if (nb > 0) {
+        const int gx = (int)((na + 127) / 128);
+        int gy = (148 * 4 + gx - 1) / gx;  // aim at four blocks per SM
+        const int max_gy = (int)((nb + DM_TILE - 1) / DM_TILE);
+        if (gy > max_gy) gy = max_gy;
+        if (gy < 1) gy = 1;
+        int slice = (int)((nb + gy - 1) / gy);
+        slice = (slice + DM_TILE - 1) / DM_TILE * DM_TILE;
+        gy = (int)((nb + slice - 1) / slice);
+        const dim3 grid((unsigned)gx, (unsigned)gy);
+        if (dim == 33)
+            desc_nn1_kernel<33><<<grid, 128, 0, s>>>(a_dev, (int)na, b_dev, (int)nb, dim, slice, packed);
+        else
+            desc_nn1_kernel<0><<<grid, 128, 0, s>>>(a_dev, (int)na, b_dev, (int)nb, dim, slice, packed);
+    }
+    desc_unpack_kernel<<<(unsigned)((na + 255) / 256), 256, 0, s>>>(packed, (int)na, out_idx_dev, out_d2_dev);
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
 }

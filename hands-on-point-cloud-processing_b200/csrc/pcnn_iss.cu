@@ -114,6 +114,7 @@ constexpr unsigned IK_NODE_MASK = 0x07ffffffu;
 struct IssArgs {
     IssThr th;
     int* cnt_pos;      // [n] neighbours within local_radius, by Morton position
+    float* wgt_pos;    // [n] 1 / cnt_pos in float (iss_detector.cpp:128), by Morton position
     float* lam_pos;    // [n] lambda3 or -1, by Morton position
     int* flag_pos;     // [n] keypoint flags, by Morton position
     float g21, g32;
@@ -159,7 +160,7 @@ __global__ void __launch_bounds__(IK_WARPS * 32) iss_pass_kernel(IndexView iv, I
             cnt++;
         } else if (PASS == ISS_COV) {
             // weight 1 / |N(j)| in float (iss_detector.cpp:128), differences in float (:131-133)
-            const float wf = A.weighted ? 1.f / (float)__ldg(A.cnt_pos + j) : 1.f;
+            const float wf = A.weighted ? __ldg(A.wgt_pos + j) : 1.f;
             const double wd = (double)wf;
             const double dx = (double)(p.x - c.x), dy = (double)(p.y - c.y), dz = (double)(p.z - c.z);
             const double wx = wd * dx, wy = wd * dy, wz = wd * dz;
@@ -271,6 +272,11 @@ __global__ void __launch_bounds__(IK_WARPS * 32) iss_pass_kernel(IndexView iv, I
     }
 }
 
+__global__ void iss_weight_kernel(const int* __restrict__ cnt_pos, int n, float* __restrict__ wgt_pos) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) wgt_pos[i] = __fdiv_rn(1.f, (float)cnt_pos[i]);  // weight_nn = 1.f / rnn_idx[idx_neighbor].size()
+}
+
 // position order -> original point order
 __global__ void iss_scatter_kernel(IndexView iv, const float* __restrict__ lam_pos, const int* __restrict__ flag_pos,
                                    float* __restrict__ lam_out, long long* __restrict__ flag_out) {
@@ -299,6 +305,7 @@ int launch_iss(const pcnn_index* ix, const pcnn_iss_params* prm, int32_t* out_id
     IssArgs A;
     long long *flag, *offsets;
     PCNN_CUDA(sc.get(&A.cnt_pos, (size_t)n));
+    PCNN_CUDA(sc.get(&A.wgt_pos, (size_t)n));
     PCNN_CUDA(sc.get(&A.lam_pos, (size_t)n));
     PCNN_CUDA(sc.get(&A.flag_pos, (size_t)n));
     PCNN_CUDA(sc.get(&flag, (size_t)n));
@@ -308,6 +315,7 @@ int launch_iss(const pcnn_index* ix, const pcnn_iss_params* prm, int32_t* out_id
     A.th = make_iss_thr(prm->local_radius);
     prof_begin(ix, s);
     iss_pass_kernel<ISS_COUNT><<<grid, IK_WARPS * 32, 0, s>>>(ix->view, A);
+    if (A.weighted) iss_weight_kernel<<<(n + 255) / 256, 256, 0, s>>>(A.cnt_pos, n, A.wgt_pos);
     iss_pass_kernel<ISS_COV><<<grid, IK_WARPS * 32, 0, s>>>(ix->view, A);
     A.th = make_iss_thr(prm->non_max_radius);
     iss_pass_kernel<ISS_NMS><<<grid, IK_WARPS * 32, 0, s>>>(ix->view, A);

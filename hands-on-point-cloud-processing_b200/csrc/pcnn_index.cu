@@ -202,6 +202,7 @@ static void free_index(pcnn_index* ix) {
     if (!ix) return;
     free_host_pipe(ix->pipe);
     if (ix->rperm) cudaFree(ix->rperm);
+    if (ix->rperm_ev) cudaEventDestroy(ix->rperm_ev);
     cudaFree(ix->pts);
     cudaFree(ix->gcode);
     cudaFree(ix->box);

@@ -55,6 +55,7 @@ struct pcnn_index {
     mutable cudaStream_t rperm_stream = nullptr;
     mutable double rperm_radius = -1.0;
     mutable double rperm_hits_per_query = -1.0;
+    mutable cudaEvent_t rperm_ev = nullptr;  // last device-side use of rperm: a writer on another stream waits for it
 };
 
 namespace pcnn {

@@ -579,30 +579,50 @@ static float run_extent(const pcnn_index* ix, double radius, bool fill, bool sta
 
 // The fill pass reuses the query ordering of the count pass before it (same stream, same query
 // buffer, same kind of ordering).  Any permutation of the queries is correct -- the ordering
-// only buys locality -- so a stale one cannot change a result.
+// only buys locality -- but it has to BE a permutation, so the one buffer is guarded: the
+// handle's mutex is held from the key check to the launch that reads (or the copy that
+// writes) it, and an event orders a writer on one stream after the last reader on another.
 static void remember_perm(const pcnn_index* ix, const unsigned* perm, const float* q, int nq, int stride, int kind,
                           double radius, cudaStream_t s) {
     std::lock_guard<std::mutex> lk(ix->rperm_mu);
     ix->rperm_kind = -1;
     ix->rperm_hits_per_query = -1.0;
     if (!perm) return;
+    if (!ix->rperm_ev && cudaEventCreateWithFlags(&ix->rperm_ev, cudaEventDisableTiming) != cudaSuccess) {
+        ix->rperm_ev = nullptr;
+        cudaGetLastError();
+        return;
+    }
     if ((size_t)nq > ix->rperm_cap) {
-        if (ix->rperm) cudaFree(ix->rperm);
+        if (ix->rperm) cudaFree(ix->rperm);  // waits for the device: no reader is left
         ix->rperm = nullptr;
         ix->rperm_cap = 0;
         if (cudaMalloc(&ix->rperm, (size_t)nq * sizeof(unsigned)) != cudaSuccess) { cudaGetLastError(); return; }
         ix->rperm_cap = (size_t)nq;
+    } else if (ix->rperm_stream != s) {
+        cudaStreamWaitEvent(s, ix->rperm_ev, 0);  // a no-op until the event has been recorded once
     }
     if (cudaMemcpyAsync(ix->rperm, perm, (size_t)nq * sizeof(unsigned), cudaMemcpyDeviceToDevice, s) != cudaSuccess) return;
+    cudaEventRecord(ix->rperm_ev, s);
     ix->rperm_q = q; ix->rperm_nq = nq; ix->rperm_stride = stride; ix->rperm_kind = kind;
     ix->rperm_stream = s; ix->rperm_radius = radius;
 }
-static const unsigned* recall_perm(const pcnn_index* ix, const float* q, int nq, int stride, int kind, cudaStream_t s) {
-    std::lock_guard<std::mutex> lk(ix->rperm_mu);
+// Returns the cached ordering with `lk` HELD when it matches (the caller launches its kernel, calls
+// perm_used() and lets go), or nullptr with `lk` released.
+static const unsigned* recall_perm(const pcnn_index* ix, const float* q, int nq, int stride, int kind, cudaStream_t s,
+                                   std::unique_lock<std::mutex>& lk) {
+    lk = std::unique_lock<std::mutex>(ix->rperm_mu);
     if (ix->rperm && ix->rperm_kind == kind && ix->rperm_q == q && ix->rperm_nq == nq && ix->rperm_stride == stride &&
         ix->rperm_stream == s)
         return ix->rperm;
+    lk.unlock();
     return nullptr;
+}
+static void perm_used(const pcnn_index* ix, cudaStream_t s, std::unique_lock<std::mutex>& lk) {
+    if (lk.owns_lock()) {
+        if (ix->rperm_ev) cudaEventRecord(ix->rperm_ev, s);
+        lk.unlock();
+    }
 }
 void note_radius_total(const pcnn_index* ix, const float* q, int64_t nq, double radius, int64_t total) {
     std::lock_guard<std::mutex> lk(ix->rperm_mu);
@@ -674,8 +694,9 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
     unsigned* perm = nullptr;
     const int method = radius_method(ix, nq, radius, true, recall_hits(ix, q, nq, radius));
     const bool batch = method == RM_BATCH || method == RM_STACK_BATCH;
+    std::unique_lock<std::mutex> perm_lock;
     if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {
-        perm = const_cast<unsigned*>(recall_perm(ix, q, nq, stride, batch ? 1 : 0, s));
+        perm = const_cast<unsigned*>(recall_perm(ix, q, nq, stride, batch ? 1 : 0, s, perm_lock));
         if (!perm) {
             int rc = batch ? sort_queries_fine(ix, q, nq, stride, ix->opt_radius_sort_bits, &perm, sc, s)
                            : sort_queries(ix, q, nq, stride, &perm, sc, s);
@@ -695,6 +716,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
             radius_stack_batch_kernel<true, false><<<bgrid, RK_WARPS * 32, 0, s>>>(
                 ix->view, q, nq, stride, perm, rt, ext, (float)radius, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
         prof_end(ix, s);
+        perm_used(ix, s, perm_lock);
         PCNN_CUDA(cudaGetLastError());
         return PCNN_OK;
     }
@@ -707,6 +729,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
             radius_stack_kernel<true, false><<<sgrid, RK_WARPS * 32, 0, s>>>(
                 ix->view, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
         prof_end(ix, s);
+        perm_used(ix, s, perm_lock);
         PCNN_CUDA(cudaGetLastError());
         return PCNN_OK;
     }
@@ -719,6 +742,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
             radius_lockstep_kernel<true, false><<<lgrid, RL_THREADS, 0, s>>>(
                 ix->view, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
         prof_end(ix, s);
+        perm_used(ix, s, perm_lock);
         PCNN_CUDA(cudaGetLastError());
         return PCNN_OK;
     }
@@ -733,6 +757,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
             radius_batch_kernel<true, false><<<bgrid, WQ_WARPS * 32, 0, s>>>(
                 ix->view, wp, q, nq, stride, perm, rt, ext, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
         prof_end(ix, s);
+        perm_used(ix, s, perm_lock);
         PCNN_CUDA(cudaGetLastError());
         return PCNN_OK;
     }
@@ -744,6 +769,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
         radius_warp_kernel<true, false><<<grid, WQ_WARPS * 32, 0, s>>>(
             ix->view, wp, q, nq, stride, perm, rt, nullptr, (const long long*)offsets, out_idx, out_dist, nullptr);
     prof_end(ix, s);
+        perm_used(ix, s, perm_lock);
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
 }

@@ -116,6 +116,7 @@ struct IssArgs {
     int* cnt_pos;      // [n] neighbours within local_radius, by Morton position
     float* wgt_pos;    // [n] 1 / cnt_pos in float (iss_detector.cpp:128), by Morton position
     float* lam_pos;    // [n] lambda3 or -1, by Morton position
+    double* cov_pos;   // [n*6] scatter matrix (a00 a01 a02 a11 a12 a22), by Morton position; a00 = NaN: < 3 neighbours
     int* flag_pos;     // [n] keypoint flags, by Morton position
     float g21, g32;
     int min_neighbors;
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(IK_WARPS * 32) iss_pass_kernel(IndexView iv, I
     bool beaten = false;
     float mine = 0.f;
     if (PASS == ISS_COV && A.cnt_pos[pos] < 3) {  // iss_detector.cpp:72
-        if (lane == 0) A.lam_pos[pos] = -1.f;
+        if (lane == 0) A.cov_pos[6 * (size_t)pos] = __longlong_as_double(0x7ff8000000000000ll);
         return;
     }
     if (PASS == ISS_NMS) {
@@ -255,21 +256,34 @@ __global__ void __launch_bounds__(IK_WARPS * 32) iss_pass_kernel(IndexView iv, I
         for (int i = 0; i < 7; i++)
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(full, v[i], o);
+        // the eigenvalues are left to iss_eigen_kernel, one THREAD per point: done here they would
+        // run on one lane of the warp (ncu: 22 % of this kernel's instructions with 1 lane active)
         if (lane == 0) {
-            double m[6] = {v[1], v[2], v[3], v[4], v[5], v[6]};
-            if (A.weighted)
-                for (int i = 0; i < 6; i++) m[i] /= v[0];  // cov /= weight_sum (iss_detector.cpp:135)
-            double ev[3];
-            sym3_eigenvalues(m, ev);
-            // float, as Eigen::Vector3f in the reference (:73-80)
-            const float l1 = (float)ev[2], l2 = (float)ev[1], l3 = (float)ev[0];
-            A.lam_pos[pos] = (l2 / l1 < A.g21 && l3 / l2 < A.g32 && l3 > 0.f) ? l3 : -1.f;
+            // cov /= weight_sum (iss_detector.cpp:135)
+            for (int i = 0; i < 6; i++) A.cov_pos[6 * (size_t)pos + i] = A.weighted ? v[1 + i] / v[0] : v[1 + i];
         }
     } else {
         cnt = __reduce_add_sync(full, cnt);
         const bool any_beaten = __any_sync(full, beaten);
         if (lane == 0) A.flag_pos[pos] = (cnt >= A.min_neighbors && !any_beaten) ? 1 : 0;
     }
+}
+
+// eigenvalues and the candidate tests (iss_detector.cpp:73-80), one thread per point
+__global__ void __launch_bounds__(128) iss_eigen_kernel(IssArgs A, int n) {
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    double m[6];
+    for (int i = 0; i < 6; i++) m[i] = A.cov_pos[6 * (size_t)pos + i];
+    float lam = -1.f;
+    if (m[0] == m[0]) {
+        double ev[3];
+        sym3_eigenvalues(m, ev);
+        // float, as Eigen::Vector3f in the reference
+        const float l1 = (float)ev[2], l2 = (float)ev[1], l3 = (float)ev[0];
+        if (l2 / l1 < A.g21 && l3 / l2 < A.g32 && l3 > 0.f) lam = l3;
+    }
+    A.lam_pos[pos] = lam;
 }
 
 __global__ void iss_weight_kernel(const int* __restrict__ cnt_pos, int n, float* __restrict__ wgt_pos) {
@@ -307,6 +321,7 @@ int launch_iss(const pcnn_index* ix, const pcnn_iss_params* prm, int32_t* out_id
     PCNN_CUDA(sc.get(&A.cnt_pos, (size_t)n));
     PCNN_CUDA(sc.get(&A.wgt_pos, (size_t)n));
     PCNN_CUDA(sc.get(&A.lam_pos, (size_t)n));
+    PCNN_CUDA(sc.get(&A.cov_pos, (size_t)n * 6));
     PCNN_CUDA(sc.get(&A.flag_pos, (size_t)n));
     PCNN_CUDA(sc.get(&flag, (size_t)n));
     PCNN_CUDA(sc.get(&offsets, (size_t)n + 1));
@@ -317,6 +332,7 @@ int launch_iss(const pcnn_index* ix, const pcnn_iss_params* prm, int32_t* out_id
     iss_pass_kernel<ISS_COUNT><<<grid, IK_WARPS * 32, 0, s>>>(ix->view, A);
     if (A.weighted) iss_weight_kernel<<<(n + 255) / 256, 256, 0, s>>>(A.cnt_pos, n, A.wgt_pos);
     iss_pass_kernel<ISS_COV><<<grid, IK_WARPS * 32, 0, s>>>(ix->view, A);
+    iss_eigen_kernel<<<(n + 127) / 128, 128, 0, s>>>(A, n);
     A.th = make_iss_thr(prm->non_max_radius);
     iss_pass_kernel<ISS_NMS><<<grid, IK_WARPS * 32, 0, s>>>(ix->view, A);
     prof_end(ix, s);

@@ -205,21 +205,37 @@ __device__ __forceinline__ bool ransac_inlier(const float* R, const float* t, co
     return __fsqrt_rn(acc) <= thr;
 }
 
-// one warp per hypothesis; best = max over (consensus << 32 | ~iteration)
-__global__ void __launch_bounds__(256) ransac_kernel(const float* __restrict__ src, const float* __restrict__ tar,
-                                                     const int32_t* __restrict__ pairs, long long np,
-                                                     unsigned long long seed, int max_iter, float thr, float coplanar_min,
-                                                     unsigned long long* __restrict__ best) {
-    __shared__ RansacHyp sh[8];
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long it = blockIdx.x * 8ll + w;
+// Two kernels: the hypotheses (sampling + SVD) one THREAD each -- on one lane of a warp they cost
+// half of a fused kernel's issue slots -- then one warp per hypothesis counts its consensus;
+// best = max over (consensus << 32 | ~iteration).
+__global__ void __launch_bounds__(128) ransac_hyp_kernel(const float* __restrict__ src, const float* __restrict__ tar,
+                                                         const int32_t* __restrict__ pairs, long long np,
+                                                         unsigned long long seed, int max_iter, float coplanar_min,
+                                                         float* __restrict__ hyp /* [max_iter][13] */) {
+    const int it = blockIdx.x * blockDim.x + threadIdx.x;
     if (it >= max_iter) return;
-    if (lane == 0) ransac_hypothesis(src, tar, pairs, np, seed, (unsigned long long)it, coplanar_min, sh[w]);
-    __syncwarp();
-    if (!sh[w].ok) return;
+    RansacHyp h;
+    ransac_hypothesis(src, tar, pairs, np, seed, (unsigned long long)it, coplanar_min, h);
+    float* o = hyp + 13 * (size_t)it;
+    o[12] = h.ok ? 1.f : 0.f;
+    if (h.ok) {
+        for (int i = 0; i < 9; i++) o[i] = h.R[i];
+        for (int i = 0; i < 3; i++) o[9 + i] = h.t[i];
+    }
+}
+
+__global__ void __launch_bounds__(256) ransac_kernel(const float* __restrict__ src, const float* __restrict__ tar,
+                                                     const int32_t* __restrict__ pairs, long long np, int max_iter,
+                                                     float thr, const float* __restrict__ hyp,
+                                                     unsigned long long* __restrict__ best) {
+    const int lane = threadIdx.x & 31;
+    const long long it = blockIdx.x * 8ll + (threadIdx.x >> 5);
+    if (it >= max_iter) return;
+    const float* hp = hyp + 13 * (size_t)it;
+    if (hp[12] == 0.f) return;
     float R[9], t[3];
-    for (int i = 0; i < 9; i++) R[i] = sh[w].R[i];
-    for (int i = 0; i < 3; i++) t[i] = sh[w].t[i];
+    for (int i = 0; i < 9; i++) R[i] = hp[i];
+    for (int i = 0; i < 3; i++) t[i] = hp[9 + i];
     int cnt = 0;
     for (long long c = lane; c < np; c += 32)
         cnt += ransac_inlier(R, t, src + 3 * (size_t)pairs[2 * c], tar + 3 * (size_t)pairs[2 * c + 1], thr) ? 1 : 0;
@@ -347,11 +363,15 @@ extern "C" int pcnn_ransac(const float* src_kp_dev, const float* tar_kp_dev, con
     Scratch sc(s);
     unsigned long long* best;
     pcnn_ransac_result* out_dev;
+    float* hyp;
     PCNN_CUDA(sc.get(&best, 1));
     PCNN_CUDA(sc.get(&out_dev, 1));
+    PCNN_CUDA(sc.get(&hyp, (size_t)prm->max_iter * 13));
     PCNN_CUDA(cudaMemsetAsync(best, 0, sizeof(unsigned long long), s));
-    ransac_kernel<<<(unsigned)((prm->max_iter + 7) / 8), 256, 0, s>>>(src_kp_dev, tar_kp_dev, pairs_dev, n_pairs, prm->seed,
-                                                                     prm->max_iter, prm->dist_threshold, prm->coplanar_min, best);
+    ransac_hyp_kernel<<<(unsigned)((prm->max_iter + 127) / 128), 128, 0, s>>>(src_kp_dev, tar_kp_dev, pairs_dev, n_pairs,
+                                                                             prm->seed, prm->max_iter, prm->coplanar_min, hyp);
+    ransac_kernel<<<(unsigned)((prm->max_iter + 7) / 8), 256, 0, s>>>(src_kp_dev, tar_kp_dev, pairs_dev, n_pairs, prm->max_iter,
+                                                                     prm->dist_threshold, hyp, best);
     ransac_final_kernel<<<1, 1, 0, s>>>(src_kp_dev, tar_kp_dev, pairs_dev, n_pairs, prm->seed, prm->coplanar_min, best, out_dev);
     PCNN_CUDA(cudaGetLastError());
     PCNN_CUDA(cudaMemcpyAsync(out_host, out_dev, sizeof(pcnn_ransac_result), cudaMemcpyDeviceToHost, s));

@@ -550,19 +550,16 @@ static RadiusThr make_thr(double radius) {
 //   (radius_lockstep_kernel), 4 = one warp per query, dense stack walk (radius_stack_kernel),
 //   5 = dense stack walk shared by a run of queries (radius_stack_batch_kernel),
 //   1 = automatic.  Measured on the 1M aggregate (count + fill kernels, ms):
-//       1M queries r=0.5:  0: 3.76+5.34   2: 2.05+4.23   3: 2.86+6.47   4: 3.34+4.90   5: 1.28+3.72
-//       1M queries r=1.0:  0: 7.27+12.7   2: 3.86+16.7                  4: 5.91+11.5   5: 2.33+14.8
+//       1M queries r=0.5:  0: 3.76+5.34   2: 2.05+4.23   3: 2.86+6.47   4: 3.34+4.90   5: 1.10+3.30
+//       1M queries r=1.0:  0: 7.27+12.7   2: 3.86+16.7                  4: 5.91+11.5   5: 2.01+10.3
 //       200k queries r=0.5: 0: 0.75+1.04  2: 0.82+1.54  3: 0.80+2.06    4: 0.65+0.94   5: 0.60+1.27
-//   so: a batch about as dense as the cloud shares walks (5), except that a fill with thousands
-//   of hits per query is dominated by contained subtrees, which the per-query kernel (4) writes
-//   with less overhead; sparse batches use 4.
+//   so: a batch about as dense as the cloud shares walks (5); sparse batches use 4.
 enum { RM_WARP = 0, RM_BATCH = 2, RM_LOCKSTEP = 3, RM_STACK = 4, RM_STACK_BATCH = 5 };
 static int radius_method(const pcnn_index* ix, int nq, double radius, bool fill, double hits_per_query) {
     int m = ix->opt_radius_batch;
     if (m == 1) {
         const bool dense = ix->opt_sort_queries && nq > 1024 && 2 * (int64_t)nq >= ix->n;
         m = dense ? RM_STACK_BATCH : RM_STACK;
-        if (fill && hits_per_query > 2000.0) m = RM_STACK;
     }
     if (m == RM_BATCH && !(radius > 1e-12 && radius < 1e12)) m = RM_WARP;
     if (m == RM_STACK_BATCH && !(radius > 1e-12 && radius < 1e12)) m = RM_STACK;

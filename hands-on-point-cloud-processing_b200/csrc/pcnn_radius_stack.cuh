@@ -256,29 +256,45 @@ radius_stack_batch_kernel(IndexView iv, const float* __restrict__ q, int nq, int
             int tcnt = 0;
             auto drain = [&]() {
                 __syncwarp();
+                // eight groups (two points per lane) per step: the per-query overhead of the inner loop --
+                // query load, cursor broadcast, loop control -- is paid once for 64 points.  A lane
+                // without a point holds +inf coordinates: its key is +inf and fails every test.
                 const int j = lane & 7;
-                for (int base = 0; base < tcnt; base += 4) {
-                    const int it = base + (lane >> 3);
+                const float INFf = __int_as_float(0x7f800000);
+                auto load = [&](int it, float4& p, bool& allhit) {
                     const unsigned ent = it < tcnt ? s_tl[w][it] : 0u;
                     const int pidx = (int)((ent & 0x7fffffffu) << PCNN_GROUP_LOG) + j;
                     const bool v = it < tcnt && pidx < iv.n;
-                    const bool allhit = v && (ent >> 31) != 0u;
-                    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+                    allhit = v && (ent >> 31) != 0u;
+                    p = make_float4(INFf, INFf, INFf, 0.f);
                     if (v) p = __ldg(iv.pts + pidx);
+                };
+                for (int base = 0; base < tcnt; base += 8) {
+                    float4 p0, p1;
+                    bool all0, all1;
+                    load(base + (lane >> 3), p0, all0);
+                    load(base + 4 + (lane >> 3), p1, all1);
                     for (int c = s0; c < e; c++) {
                         const float4 cq = s_q[w][c];
-                        const float dx = p.x - cq.x, dy = p.y - cq.y, dz = p.z - cq.z;
-                        const float s = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-                        bool hit = allhit || (v && s <= t_in);
-                        if (v && !hit && !(s > t_out))  // the sliver between the float thresholds
-                            hit = key64(p.x, p.y, p.z, (double)cq.x, (double)cq.y, (double)cq.z) <= thr;
-                        const unsigned m = __ballot_sync(full, hit);
-                        if constexpr (FILL) {
-                            if (m == 0) continue;
-                            const long long ro = __shfl_sync(full, run, c);
-                            if (hit) put(ro + __popc(m & lt), p, cq, s);
+                        const float ax = p0.x - cq.x, ay = p0.y - cq.y, az = p0.z - cq.z;
+                        const float bx = p1.x - cq.x, by = p1.y - cq.y, bz = p1.z - cq.z;
+                        const float sa = fmaf(ax, ax, fmaf(ay, ay, az * az));
+                        const float sb = fmaf(bx, bx, fmaf(by, by, bz * bz));
+                        bool h0 = all0 || sa <= t_in, h1 = all1 || sb <= t_in;
+                        const bool amb0 = !h0 && !(sa > t_out), amb1 = !h1 && !(sb > t_out);
+                        if (__any_sync(full, amb0 || amb1)) {  // the sliver between the float thresholds: rare
+                            if (amb0) h0 = key64(p0.x, p0.y, p0.z, (double)cq.x, (double)cq.y, (double)cq.z) <= thr;
+                            if (amb1) h1 = key64(p1.x, p1.y, p1.z, (double)cq.x, (double)cq.y, (double)cq.z) <= thr;
                         }
-                        if (lane == c) run += __popc(m);
+                        const unsigned m0 = __ballot_sync(full, h0), m1 = __ballot_sync(full, h1);
+                        const int n0 = __popc(m0), n1 = __popc(m1);
+                        if constexpr (FILL) {
+                            if ((m0 | m1) == 0u) continue;
+                            const long long ro = __shfl_sync(full, run, c);
+                            if (h0) put(ro + __popc(m0 & lt), p0, cq, sa);
+                            if (h1) put(ro + n0 + __popc(m1 & lt), p1, cq, sb);
+                        }
+                        if (lane == c) run += n0 + n1;
                     }
                 }
                 tcnt = 0;
@@ -325,15 +341,18 @@ radius_stack_batch_kernel(IndexView iv, const float* __restrict__ q, int nq, int
                         const int cL = __shfl_sync(full, L, b), cn = __shfl_sync(full, nd, b);
                         const int p0 = (cn << cL) << PCNN_GROUP_LOG;
                         const int p1 = min(((cn + 1) << cL) << PCNN_GROUP_LOG, iv.n);
-                        for (int pb = p0; pb < p1; pb += 32) {
-                            const bool v = pb + lane < p1;
-                            float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if (v) p = __ldg(iv.pts + pb + lane);
+                        for (int pb = p0; pb < p1; pb += 64) {  // 64 points per step, two per lane
+                            const bool va = pb + lane < p1, vb = pb + 32 + lane < p1;
+                            float4 pa = make_float4(0.f, 0.f, 0.f, 0.f), pbv = pa;
+                            if (va) pa = __ldg(iv.pts + pb + lane);
+                            if (vb) pbv = __ldg(iv.pts + pb + 32 + lane);
                             for (int c = s0; c < e; c++) {
                                 const float4 cq = s_q[w][c];
-                                const long long ro = __shfl_sync(full, run, c) + (pb - p0);
-                                const float dx = p.x - cq.x, dy = p.y - cq.y, dz = p.z - cq.z;
-                                if (v) put(ro + lane, p, cq, fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+                                const long long ro = __shfl_sync(full, run, c) + (pb - p0) + lane;
+                                const float ax = pa.x - cq.x, ay = pa.y - cq.y, az = pa.z - cq.z;
+                                const float bx = pbv.x - cq.x, by = pbv.y - cq.y, bz = pbv.z - cq.z;
+                                if (va) put(ro, pa, cq, fmaf(ax, ax, fmaf(ay, ay, az * az)));
+                                if (vb) put(ro + 32, pbv, cq, fmaf(bx, bx, fmaf(by, by, bz * bz)));
                             }
                         }
                         if (mine) run += p1 - p0;

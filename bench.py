@@ -486,7 +486,7 @@ def run_gpu(args):
     e2e = {"value": world * N_QUERIES * args.steps / e2e_s, "unit": "queries/s",
            "h2d_bytes_per_step": int(h_q.nbytes), "d2h_bytes_per_step": int(h_idx.nbytes + h_dist.nbytes),
            "ms_per_step": 1e3 * e2e_s / args.steps,
-           "api": "pcnn_knn_host (C ABI), pinned host buffers, 3-stream chunked pipeline"}
+           "api": "pcnn_knn_host (C ABI), pinned host buffers, 8 stages on 8 streams"}
     assert np.array_equal(h_idx, o_idx.cpu().numpy()), "host and device entry points disagree"
 
     # ---- roofline of the dominant kernel (knn_dfs_kernel<8>)

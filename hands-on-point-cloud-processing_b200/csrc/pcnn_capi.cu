@@ -1,22 +1,24 @@
 // pcnn_capi.cu -- C ABI entry points for kNN / radius search (declared in include/pcnn.h).
 // Device-pointer variants validate and enqueue; host-pointer variants stage through HBM in
-// chunks on three streams so that the PCIe copies of one chunk overlap the kernels of the
+// stages on up to eight streams so that the PCIe copies of one chunk overlap the kernels of the
 // next (the reference has no device boundary: Homework2/hw2/include/benchmark.hpp:59-72).
 #include <algorithm>
 #include <cstdlib>
 #include <vector>
 #include "pcnn_internal.cuh"
+#include <chrono>
+#include <vector>
 
 using namespace pcnn;
 
 // Streams and device staging buffers of the host-pointer entry points; one per index handle,
 // created on first use, grown on demand, freed with the handle.
-constexpr int HOST_STREAMS = 3;
+constexpr int HOST_STREAMS = 8;
 struct HostPipe {
-    cudaStream_t s[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+    cudaStream_t s[HOST_STREAMS] = {};
     pcnn::DevBuf q[HOST_STREAMS], idx[HOST_STREAMS], d32[HOST_STREAMS], d64[HOST_STREAMS];
     pcnn::DevBuf off;  // radius: CSR offsets
-    cudaEvent_t ev[HOST_STREAMS] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev[HOST_STREAMS] = {};
 };
 
 namespace pcnn {
@@ -35,13 +37,17 @@ void free_host_pipe(HostPipe* hp) {
 namespace {
 
 // pipeline stage size: enough stages to hide the PCIe copies behind the kernels, few enough
-// that the ~14 launches per stage stay negligible
+// that the ~14 launches per stage (70 us of host time) stay ahead of the device.  Measured
+// with PCNN_PIPE_TRACE on 1M queries, k = 8: 4 stages on 3 streams 1.88 ms, 8 stages on 8
+// streams 1.75 ms (the result copy then runs back to back from the end of the first stage, at
+// 50 GB/s, and the searches keep just ahead of it); shorter first stages gain nothing because
+// the query ordering of a stage is launch-latency bound (~0.2 ms whatever its size).
 int64_t host_chunk(int64_t nq) {
     if (const char* e = std::getenv("PCNN_HOST_CHUNK")) {  // tuning aid
         const long long v = std::atoll(e);
         if (v > 0) return std::min<int64_t>(v, nq);
     }
-    int64_t c = (nq + 3) / 4;
+    int64_t c = (nq + 7) / 8;
     c = std::max<int64_t>(c, 1 << 16);
     c = std::min<int64_t>(c, 1 << 18);
     return std::min(c, nq);
@@ -107,7 +113,9 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
     rc = get_pipe(ix, &hp, "pcnn_knn_host");
     if (rc != PCNN_OK) return rc;
     const int64_t chunk = host_chunk(nq);
-    const int nstreams = (int)std::min<int64_t>(HOST_STREAMS, (nq + chunk - 1) / chunk);
+    int max_streams = HOST_STREAMS;
+    if (const char* ev = std::getenv("PCNN_HOST_STREAMS")) max_streams = std::max(1, std::min(HOST_STREAMS, std::atoi(ev)));  // tuning aid
+    const int nstreams = (int)std::min<int64_t>(max_streams, (nq + chunk - 1) / chunk);
     cudaError_t e = cudaSuccess;
     for (int i = 0; i < nstreams && e == cudaSuccess; i++) {
         e = hp->q[i].ensure(sizeof(float) * (size_t)chunk * stride);
@@ -119,10 +127,25 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
         set_error("pcnn_knn_host: staging allocation failed: %s", cudaGetErrorString(e));
         return PCNN_ERR_NOMEM;
     }
+    // PCNN_PIPE_TRACE=1 (tuning aid): per-stage event times of this call on stderr
+    static const bool trace = std::getenv("PCNN_PIPE_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    std::vector<double> thost;
+    const auto t_host0 = std::chrono::steady_clock::now();
+    auto mark = [&](cudaStream_t st) {
+        if (!trace) return;
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        cudaEventRecord(ev, st);
+        tev.push_back(ev);
+        thost.push_back(std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_host0).count());
+    };
+    mark(hp->s[0]);
     int c = 0;
-    for (int64_t q0 = 0; q0 < nq && rc == PCNN_OK; q0 += chunk, c++) {
+    int64_t m = 0;
+    for (int64_t q0 = 0; q0 < nq && rc == PCNN_OK; q0 += m, c++) {
         const int b = c % nstreams;
-        const int64_t m = std::min<int64_t>(chunk, nq - q0);
+        m = std::min<int64_t>(chunk, nq - q0);
         cudaStream_t s = hp->s[b];
         float* dq = (float*)hp->q[b].p;
         int32_t* di = (int32_t*)hp->idx[b].p;
@@ -130,14 +153,17 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
         double* dd64 = out_dist64_host ? (double*)hp->d64[b].p : nullptr;
         e = cudaMemcpyAsync(dq, q_host + q0 * stride, sizeof(float) * (size_t)m * stride, cudaMemcpyHostToDevice, s);
         if (e != cudaSuccess) { set_error("pcnn_knn_host: H2D failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; break; }
+        mark(s);
         rc = launch_knn(index, dq, m, stride, k, di, dd, dd64, s);
         if (rc != PCNN_OK) break;
+        mark(s);
         e = cudaMemcpyAsync(out_idx_host + q0 * k, di, sizeof(int32_t) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && out_dist_host)
             e = cudaMemcpyAsync(out_dist_host + q0 * k, dd, sizeof(float) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && out_dist64_host)
             e = cudaMemcpyAsync(out_dist64_host + q0 * k, dd64, sizeof(double) * (size_t)m * k, cudaMemcpyDeviceToHost, s);
         if (e != cudaSuccess) { set_error("pcnn_knn_host: D2H failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; }
+        mark(s);
     }
     for (int i = 0; i < nstreams; i++) {
         e = cudaStreamSynchronize(hp->s[i]);
@@ -145,6 +171,17 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
             set_error("pcnn_knn_host: device work failed: %s", cudaGetErrorString(e));
             rc = PCNN_ERR_CUDA;
         }
+    }
+    if (trace) {
+        const double t_end = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_host0).count();
+        std::fprintf(stderr, "pcnn_knn_host trace (ms since call; device | host enqueue), call returned at %.3f\n", t_end);
+        for (size_t i = 1; i < tev.size(); i++) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, tev[0], tev[i]);
+            static const char* what[3] = {"H2D done", "search done", "D2H done"};
+            std::fprintf(stderr, "  stage %zu %-11s %7.3f | %7.3f\n", (i - 1) / 3, what[(i - 1) % 3], ms, thost[i]);
+        }
+        for (cudaEvent_t ev : tev) cudaEventDestroy(ev);
     }
     return rc;
 }

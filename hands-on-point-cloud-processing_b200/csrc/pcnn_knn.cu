@@ -84,6 +84,9 @@ constexpr int KT_THREADS = 128;
 #ifndef PCNN_DFS_MINBLOCKS
 #define PCNN_DFS_MINBLOCKS 8  // resident blocks per SM asked of ptxas for knn_dfs_kernel (64 registers; measured)
 #endif
+#ifndef PCNN_DFS_MINBLOCKS16
+#define PCNN_DFS_MINBLOCKS16 6  // the same for the K = 16 instance (80 registers): 1M x 1M, k = 10: 8 -> 2.33 ms, 6 -> 2.23, 5 -> 2.35, 4 -> 2.53
+#endif
 
 template <int K>
 __device__ __forceinline__ void write_row(const TopK<K>& tk, int64_t row, int k, int32_t* out_idx,
@@ -671,7 +674,7 @@ knn_lockstep_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
 // lock step (fixed rounds of predicated steps), groups a lane needs go to its queue and the
 // queues are drained together, as in knn_lockstep_kernel.
 template <int K>
-__global__ void __launch_bounds__(KT_THREADS, PCNN_DFS_MINBLOCKS)
+__global__ void __launch_bounds__(KT_THREADS, K <= 8 ? PCNN_DFS_MINBLOCKS : PCNN_DFS_MINBLOCKS16)
 knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
                float* __restrict__ out_dist, double* __restrict__ out_dist64,

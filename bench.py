@@ -366,9 +366,11 @@ def extras(ix, pc, torch, dev, pts, nrm, qry, d_q):
 
 
 def icp_sharded(ix, pc, torch, dist, dev, nrm, qry, world, rank):
-    """C4: point-to-plane ICP, 1M x 1M, source sharded over the ranks; per iteration one fused
-    accumulate kernel, an all-reduce of the 31 partial sums (+ a 1-element MAX), and the
-    replicated on-device solve.  No host synchronisation inside the loop."""
+    """C4: point-to-plane ICP, 1M x 1M, source sharded over the ranks.  Two forms, both without
+    host synchronisation inside the loop: the fused one (pcnn_icp_step_peer: one kernel per
+    iteration does accumulate + all-reduce through peer memory + replicated solve) and the
+    split-phase one with NCCL (accumulate kernel, all-reduce of the 31 sums + a 1-element MAX,
+    update kernel)."""
     n = N_QUERIES
     d_src = torch.empty((n, 3), dtype=torch.float32, device=dev)
     d_nrm = torch.empty((N_POINTS, 3), dtype=torch.float32, device=dev)
@@ -379,28 +381,48 @@ def icp_sharded(ix, pc, torch, dist, dev, nrm, qry, world, rank):
     dist.broadcast(d_src, 0)
     dist.broadcast(d_nrm, 0)
     lo, hi = pc.shard_range(n, world, rank)
-    res = None
-    for iters in (2, 30):  # warm-up, then timed
+
+    def run(iters, fused):
         st = pc.IcpState(ix, d_src[lo:hi].contiguous(), tar_normals=d_nrm, max_iter=iters, mode=1,
                          src_index_base=lo)
+        if fused:
+            st.attach_peers(dist)
         dist.barrier()
         torch.cuda.synchronize()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         for _ in range(iters):
-            st.accumulate()
-            pc.allreduce_icp_sums(st.sums, dist)
-            st.update()
+            if fused:
+                st.step_peer()           # ONE kernel: accumulate + peer-mailbox all-reduce + solve
+            else:
+                st.accumulate()
+                pc.allreduce_icp_sums(st.sums, dist)
+                st.update()
         ev1.record()
         torch.cuda.synchronize()
         t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         res = st.finish()
         st.close()
-        ms = float(t.item())
-    return {"iters_per_s": res["iters"] / (ms * 1e-3), "iters": res["iters"], "ms_total": ms,
-            "pairs": res["pairs"], "status": res["status"], "n_gpus": world,
-            "collective": "NCCL all-reduce of 31 doubles (SUM) + 1 int64 (MAX) per iteration"}
+        return res, float(t.item())
+
+    out = {"n_gpus": world}
+    for fused, name in ((True, "fused_peer"), (False, "nccl_split_phase")):
+        try:
+            run(2, fused)                # warm-up
+            res, ms = run(30, fused)
+        except pc.PcnnError as exc:      # e.g. no CUDA IPC between the ranks: keep the NCCL form
+            out[name] = {"error": str(exc)}
+            continue
+        out[name] = {"iters_per_s": res["iters"] / (ms * 1e-3), "iters": res["iters"], "ms_total": ms,
+                     "us_per_iter": 1e3 * ms / max(res["iters"], 1), "pairs": res["pairs"], "status": res["status"],
+                     "T": [float(x) for x in res["T"].reshape(-1)]}
+    out["iters_per_s"] = out["fused_peer"].get("iters_per_s", out["nccl_split_phase"].get("iters_per_s"))
+    out["collective"] = ("fused_peer: the last block of each rank stores its 32 sums into every peer's mailbox over "
+                         "NVLink (P2P stores + system-scope flag) and adds the world's in rank order, inside the "
+                         "iteration kernel; nccl_split_phase: accumulate kernel, NCCL all-reduce of 31 doubles (SUM) "
+                         "+ 1 int64 (MAX), update kernel")
+    return out
 
 
 # ---------------------------------------------------------------------------- GPU side

@@ -28,6 +28,7 @@ KDTREE, OCTREE = 0, 1
 OK, ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_CAPACITY = 0, -1, -2, -3, -4, -5
 MAX_K = 128
 ICP_NSUMS = 32
+ICP_PEER_HANDLE_BYTES = 64  # PCNN_ICP_PEER_HANDLE_BYTES
 
 
 class PcnnError(RuntimeError):
@@ -76,6 +77,7 @@ EXPORTS = [
     "pcnn_release_cached", "pcnn_debug_warp_times", "pcnn_iss_detect", "pcnn_iss_detect_host",
     "pcnn_voxel_downsample", "pcnn_estimate_normals", "pcnn_estimate_normals_host",
     "pcnn_desc_nn1", "pcnn_match_descriptors", "pcnn_ransac",
+    "pcnn_icp_peer_export", "pcnn_icp_peer_attach", "pcnn_icp_step_peer", "pcnn_icp_peer_detach",
 ]
 
 
@@ -113,6 +115,10 @@ def lib():
     L.pcnn_icp_update.argtypes = [vp, vp]
     L.pcnn_icp_finish.argtypes = [vp, C.POINTER(IcpResult), vp]
     L.pcnn_icp_destroy.argtypes = [vp]
+    L.pcnn_icp_peer_export.argtypes = [vp, vp, C.POINTER(vp)]
+    L.pcnn_icp_peer_attach.argtypes = [vp, i32, i32, vp, C.POINTER(vp)]
+    L.pcnn_icp_step_peer.argtypes = [vp, vp]
+    L.pcnn_icp_peer_detach.argtypes = [vp]
     L.pcnn_nn1_f32.argtypes = [vp, vp, i64, i32, vp, vp, vp]
     L.pcnn_release_cached.argtypes = [i32]
     L.pcnn_debug_warp_times.argtypes = [vp, vp]

@@ -35,6 +35,12 @@ struct pcnn_icp_state {
     // pcnn_icp_create and goes back to it on the same stream: no device-wide synchronisation per
     // registration (cudaMalloc/cudaFree cost 50 ms per call next to a few GB of cached blocks)
     cudaStream_t mem_stream = nullptr;
+    // peer exchange (pcnn_icp_step_peer): this rank's mailbox (cudaMalloc: IPC-exportable) and the
+    // peers' mailboxes as mapped into this process
+    struct PeerBox* box = nullptr;
+    struct PeerBox* peer[PCNN_ICP_MAX_PEERS] = {};
+    bool peer_ipc[PCNN_ICP_MAX_PEERS] = {};
+    int rank = 0, world = 0;
 };
 
 namespace pcnn {
@@ -60,6 +66,18 @@ struct Dev {
     float loss;
     long long last_pairs;
     unsigned block_counter;
+    unsigned long long peer_seq;  // iterations exchanged so far (identical on every rank)
+};
+
+// One per rank, in that rank's memory; peers store into it.  Two slots: a rank can be at most
+// one iteration ahead of the slowest peer (it needs that peer's flag of iteration i to finish i).
+struct PeerBox {
+    double sums[2][PCNN_ICP_MAX_PEERS][PCNN_ICP_NSUMS];
+    unsigned long long flag[2][PCNN_ICP_MAX_PEERS];
+};
+struct PeerView {
+    PeerBox* box[PCNN_ICP_MAX_PEERS];
+    int rank, world;
 };
 
 namespace pcnn {
@@ -193,14 +211,65 @@ __device__ __forceinline__ long long warp_max_ll(long long v) {
     return v;
 }
 
+// All-reduce of the folded sums through the peers' mailboxes, executed by warp 0 of the last block
+// (lane = column).  Stores to every peer, system fence, release of the sequence flag; acquire of
+// the flags in the own mailbox; contributions added in rank order: bit-identical on every rank.
+__device__ double peer_exchange(const PeerView& pv, Dev* st, int col, double r) {
+    const unsigned long long seq = st->peer_seq + 1;
+    const int slot = (int)(seq & 1);
+    for (int p = 0; p < pv.world; p++) {
+        double* dst = &pv.box[p]->sums[slot][pv.rank][col];
+        asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(dst), "d"(r) : "memory");
+    }
+    __threadfence_system();
+    __syncwarp();
+    if (col < pv.world) {
+        unsigned long long* f = &pv.box[col]->flag[slot][pv.rank];
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(seq) : "memory");
+    }
+    PeerBox* mine = pv.box[pv.rank];
+    bool ok = true;
+    if (col < pv.world) {
+        const unsigned long long* f = &mine->flag[slot][col];
+        unsigned long long t0, t1, v;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+            if (v >= seq) break;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > (unsigned long long)PCNN_ICP_PEER_TIMEOUT_MS * 1000000ull) { ok = false; break; }
+            __nanosleep(200);
+        }
+    }
+    ok = __all_sync(0xffffffffu, ok);
+    double tot = 0.0;
+    long long m = 0;
+    if (ok) {
+        for (int j = 0; j < pv.world; j++) {
+            double x;
+            asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(x) : "l"(&mine->sums[slot][j][col]) : "memory");
+            if (col == 31) { const long long xi = __double_as_longlong(x); m = (j == 0 || xi > m) ? xi : m; }
+            else tot += x;
+        }
+        if (col == 31) tot = __longlong_as_double(m);
+    } else {
+        tot = r;
+        if (col == 0) { st->status = 2; st->done = 1; }
+    }
+    if (col == 0) st->peer_seq = seq;
+    return tot;
+}
+
 // MODE 0 = point-to-point (16 sums), 1 = point-to-plane (29 sums).
+// KIND 0 = split phase (sums only), 1 = fused update, 2 = fused peer all-reduce + update.
 // Blocks walk the source cloud with a grid stride (whole warps: tail lanes shadow the last
 // point and contribute nothing), each thread keeps its sums in registers across its points.
-template <int MODE, bool FUSED>
+template <int MODE, int KIND>
 __global__ void __launch_bounds__(ICP_THREADS)
 icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __restrict__ nrm,
                       int* __restrict__ prev, int n_src, float max_corres_dist, float loss_epsilon,
-                      Dev* __restrict__ st, double* __restrict__ partials) {
+                      Dev* __restrict__ st, double* __restrict__ partials, const PeerView pv) {
+    constexpr bool FUSED = KIND != 0;
     constexpr int NT = MODE == 0 ? 16 : 29;
     __shared__ double s_part[ICP_THREADS / 32][ICP_NS];
     __shared__ long long s_last[ICP_THREADS / 32];
@@ -361,6 +430,7 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
         } else {
             r = ((s_part[0][col] + s_part[1][col]) + s_part[2][col]) + s_part[3][col];
         }
+        if (KIND == 2) r = peer_exchange(pv, st, col, r);
         st->sums[col] = r;
     }
     __syncthreads();
@@ -420,6 +490,7 @@ __global__ void icp_state_init_kernel(Dev* st, const float* __restrict__ T0) {
         for (int i = 0; i < ICP_NS; i++) st->sums[i] = 0.0;
         st->iters = 0; st->converged = 0; st->status = 0; st->done = 0; st->unchanged = 0;
         st->last_loss = 0.f; st->loss = 0.f; st->last_pairs = 0; st->block_counter = 0;
+        st->peer_seq = 0;
     }
 }
 
@@ -456,23 +527,44 @@ int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     return PCNN_OK;
 }
 
+static void icp_peer_detach(pcnn_icp_state* st) {
+    for (int p = 0; p < PCNN_ICP_MAX_PEERS; p++) {
+        if (st->peer[p] && st->peer_ipc[p]) cudaIpcCloseMemHandle(st->peer[p]);
+        st->peer[p] = nullptr;
+        st->peer_ipc[p] = false;
+    }
+    st->world = 0;
+}
+
 static void icp_free(pcnn_icp_state* st) {
     if (!st) return;
+    icp_peer_detach(st);
+    if (st->box) cudaFree(st->box);
     void* ptrs[5] = {st->cur, st->nrm, st->prev, st->partials, st->dev};
     for (void* p : ptrs)
         if (p) cudaFreeAsync(p, st->mem_stream);
     delete st;
 }
 
-static int icp_launch_accumulate(pcnn_icp_state* st, bool fused, cudaStream_t s) {
-    if (st->n_src == 0) return PCNN_OK;
+// kind: 0 = sums only, 1 = fused update, 2 = fused peer all-reduce + update (a rank without
+// source points still takes part in the exchange with one block and zero sums)
+static int icp_launch_accumulate(pcnn_icp_state* st, int kind, cudaStream_t s) {
+    if (st->n_src == 0 && kind != 2) return PCNN_OK;
     const pcnn_index* ix = st->target;
     const int n = (int)st->n_src;
-#define PCNN_ICP_LAUNCH(MODE, FUSED)                                                             \
-    icp_accumulate_kernel<MODE, FUSED><<<st->nblocks, ICP_THREADS, 0, s>>>(                      \
-        ix->view, st->cur, st->nrm, st->prev, n, st->prm.max_corres_dist, st->prm.loss_epsilon, st->dev, st->partials)
-    if (st->prm.mode == 0) { if (fused) PCNN_ICP_LAUNCH(0, true); else PCNN_ICP_LAUNCH(0, false); }
-    else { if (fused) PCNN_ICP_LAUNCH(1, true); else PCNN_ICP_LAUNCH(1, false); }
+    PeerView pv{};
+    if (kind == 2) {
+        for (int p = 0; p < st->world; p++) pv.box[p] = st->peer[p];
+        pv.rank = st->rank; pv.world = st->world;
+    }
+#define PCNN_ICP_LAUNCH(MODE, KIND)                                                              \
+    icp_accumulate_kernel<MODE, KIND><<<st->nblocks, ICP_THREADS, 0, s>>>(                       \
+        ix->view, st->cur, st->nrm, st->prev, n, st->prm.max_corres_dist, st->prm.loss_epsilon, st->dev, st->partials, pv)
+    if (st->prm.mode == 0) {
+        if (kind == 2) PCNN_ICP_LAUNCH(0, 2); else if (kind == 1) PCNN_ICP_LAUNCH(0, 1); else PCNN_ICP_LAUNCH(0, 0);
+    } else {
+        if (kind == 2) PCNN_ICP_LAUNCH(1, 2); else if (kind == 1) PCNN_ICP_LAUNCH(1, 1); else PCNN_ICP_LAUNCH(1, 0);
+    }
 #undef PCNN_ICP_LAUNCH
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
@@ -567,10 +659,88 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
 int pcnn_icp_accumulate(pcnn_icp_state* st, pcnn_stream stream) {
     PCNN_CHECK_ARG(st, "pcnn_icp_accumulate: NULL state");
     DeviceGuard g(st->device);
-    return icp_launch_accumulate(st, false, (cudaStream_t)stream);
+    return icp_launch_accumulate(st, 0, (cudaStream_t)stream);
 }
 
 double* pcnn_icp_sums_dev(pcnn_icp_state* st) { return st ? st->dev->sums : nullptr; }
+
+int pcnn_icp_peer_export(pcnn_icp_state* st, void* handle_out, void** mailbox_dev_out) {
+    PCNN_CHECK_ARG(st, "pcnn_icp_peer_export: NULL state");
+    DeviceGuard g(st->device);
+    if (!st->box) {
+        // cudaMalloc, not the stream-ordered pool: pool memory cannot be exported over CUDA IPC
+        PeerBox* b = nullptr;
+        PCNN_CUDA(cudaMalloc(&b, sizeof(PeerBox)));
+        cudaError_t e = cudaMemset(b, 0, sizeof(PeerBox));
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { cudaFree(b); set_error("pcnn_icp_peer_export: %s", cudaGetErrorString(e)); return PCNN_ERR_CUDA; }
+        st->box = b;
+    }
+    if (handle_out) {
+        static_assert(sizeof(cudaIpcMemHandle_t) == PCNN_ICP_PEER_HANDLE_BYTES, "IPC handle size");
+        PCNN_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle_out), st->box));
+    }
+    if (mailbox_dev_out) *mailbox_dev_out = st->box;
+    return PCNN_OK;
+}
+
+int pcnn_icp_peer_attach(pcnn_icp_state* st, int rank, int world, const void* handles, void* const* ptrs) {
+    PCNN_CHECK_ARG(st, "pcnn_icp_peer_attach: NULL state");
+    PCNN_CHECK_ARG(world >= 1 && world <= PCNN_ICP_MAX_PEERS && rank >= 0 && rank < world,
+                   "pcnn_icp_peer_attach: need 0 <= rank < world <= PCNN_ICP_MAX_PEERS");
+    PCNN_CHECK_ARG(st->box, "pcnn_icp_peer_attach: call pcnn_icp_peer_export first");
+    PCNN_CHECK_ARG(world == 1 || handles || ptrs, "pcnn_icp_peer_attach: neither handles nor pointers given");
+    PCNN_CHECK_ARG(st->target && st->target->n > 0, "pcnn_icp_peer_attach: empty target cloud");
+    DeviceGuard g(st->device);
+    icp_peer_detach(st);
+    for (int p = 0; p < world; p++) {
+        if (p == rank) { st->peer[p] = st->box; continue; }
+        if (ptrs) {
+            PCNN_CHECK_ARG(ptrs[p], "pcnn_icp_peer_attach: NULL peer pointer");
+            cudaPointerAttributes at{};
+            PCNN_CUDA(cudaPointerGetAttributes(&at, ptrs[p]));
+            if (at.type == cudaMemoryTypeDevice && at.device != st->device) {
+                const cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                    icp_peer_detach(st);
+                    set_error("pcnn_icp_peer_attach: no peer access %d -> %d: %s", st->device, at.device, cudaGetErrorString(e));
+                    return PCNN_ERR_CUDA;
+                }
+                cudaGetLastError();
+            }
+            st->peer[p] = static_cast<PeerBox*>(ptrs[p]);
+        } else {
+            cudaIpcMemHandle_t h;
+            std::memcpy(&h, static_cast<const char*>(handles) + (size_t)p * PCNN_ICP_PEER_HANDLE_BYTES, sizeof(h));
+            void* ptr = nullptr;
+            const cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                icp_peer_detach(st);
+                set_error("pcnn_icp_peer_attach: cannot map the mailbox of rank %d: %s", p, cudaGetErrorString(e));
+                return PCNN_ERR_CUDA;
+            }
+            st->peer[p] = static_cast<PeerBox*>(ptr);
+            st->peer_ipc[p] = true;
+        }
+    }
+    st->rank = rank; st->world = world;
+    return PCNN_OK;
+}
+
+int pcnn_icp_step_peer(pcnn_icp_state* st, pcnn_stream stream) {
+    PCNN_CHECK_ARG(st, "pcnn_icp_step_peer: NULL state");
+    PCNN_CHECK_ARG(st->world >= 1, "pcnn_icp_step_peer: call pcnn_icp_peer_attach first");
+    DeviceGuard g(st->device);
+    return icp_launch_accumulate(st, 2, (cudaStream_t)stream);
+}
+
+int pcnn_icp_peer_detach(pcnn_icp_state* st) {
+    PCNN_CHECK_ARG(st, "pcnn_icp_peer_detach: NULL state");
+    DeviceGuard g(st->device);
+    cudaDeviceSynchronize();
+    icp_peer_detach(st);
+    return PCNN_OK;
+}
 
 int pcnn_icp_update(pcnn_icp_state* st, pcnn_stream stream) {
     PCNN_CHECK_ARG(st, "pcnn_icp_update: NULL state");
@@ -622,7 +792,7 @@ int pcnn_icp(const pcnn_index* target, const float* tar_normals_dev, const float
         const bool timed = cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
         if (timed) cudaEventRecord(e0, (cudaStream_t)stream);
         for (int it = 0; it < params->max_iter && rc == PCNN_OK; it++)
-            rc = icp_launch_accumulate(st, true, (cudaStream_t)stream);  // fused update, no host sync
+            rc = icp_launch_accumulate(st, 1, (cudaStream_t)stream);  // fused update, no host sync
         if (timed) cudaEventRecord(e1, (cudaStream_t)stream);
         if (rc == PCNN_OK) rc = pcnn_icp_finish(st, out_host, stream);  // waits for the stream
         if (rc == PCNN_OK && timed) cudaEventElapsedTime(&out_host->loop_ms, e0, e1);

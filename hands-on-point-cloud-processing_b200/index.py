@@ -253,8 +253,51 @@ class IcpState:
         _check(lib().pcnn_icp_finish(self._h, C.byref(res), _stream()))
         return _icp_dict(res)
 
+    # ---- fused accumulate + all-reduce + update over peer memory (NVLink), one kernel per iteration
+    def export_mailbox(self):
+        """(64-byte CUDA IPC handle, device pointer) of this rank's mailbox (pcnn_icp_peer_export)."""
+        handle = (C.c_ubyte * api.ICP_PEER_HANDLE_BYTES)()
+        ptr = C.c_void_p()
+        _check(lib().pcnn_icp_peer_export(self._h, handle, C.byref(ptr)))
+        return bytes(handle), ptr.value
+
+    def attach_peers(self, dist, group=None):
+        """One process per GPU: exchange the mailbox handles through ``dist`` (host-side, once) and
+        map every peer's mailbox.  After this, ``step_peer()`` needs no collective call."""
+        import torch
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        handle, _ = self.export_mailbox()
+        mine = torch.frombuffer(bytearray(handle), dtype=torch.uint8)
+        backend = dist.get_backend(group)
+        dev = self._keep[0].device if backend == "nccl" else torch.device("cpu")
+        bufs = [torch.empty(api.ICP_PEER_HANDLE_BYTES, dtype=torch.uint8, device=dev) for _ in range(world)]
+        dist.all_gather(bufs, mine.to(dev), group=group)
+        blob = b"".join(bytes(b.cpu().numpy().tobytes()) for b in bufs)
+        arr = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        _check(lib().pcnn_icp_peer_attach(self._h, rank, world, arr, None))
+        self._peers = (dist, group)
+
+    def attach_local_peers(self, rank, mailbox_ptrs):
+        """Same process (several GPUs driven by one process, or tests): peers by device pointer."""
+        world = len(mailbox_ptrs)
+        arr = (C.c_void_p * world)(*[C.c_void_p(p) for p in mailbox_ptrs])
+        _check(lib().pcnn_icp_peer_attach(self._h, rank, world, None, arr))
+
+    def step_peer(self):
+        _check(lib().pcnn_icp_step_peer(self._h, _stream()))
+
+    def detach_peers(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            _check(lib().pcnn_icp_peer_detach(self._h))
+        peers = getattr(self, "_peers", None)
+        if peers is not None:
+            peers[0].barrier(group=peers[1])  # every rank unmaps before any rank frees its mailbox
+            self._peers = None
+
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:
+            if getattr(self, "_peers", None) is not None:
+                self.detach_peers()
             lib().pcnn_icp_destroy(self._h)
             self._h = C.c_void_p()
 

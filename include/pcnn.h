@@ -187,7 +187,8 @@ typedef struct {
     float T[16];       /* row-major 4x4 T_total: R = T[0..2][0..2], t = T[0..2][3] */
     int32_t iters;     /* iterations whose update was applied */
     int32_t converged; /* 1 if the unchanged-loss rule fired */
-    int32_t status;    /* 0 ok; 1 = an iteration had no correspondences or a singular system */
+    int32_t status;    /* 0 ok; 1 = an iteration had no correspondences or a singular system;
+                          2 = a peer did not answer in time (pcnn_icp_step_peer) */
     float last_loss;
     int64_t last_pairs; /* correspondences kept in the last executed iteration */
     float loop_ms;      /* pcnn_icp / pcnn_icp_host: device time of the iteration loop alone
@@ -221,6 +222,37 @@ double* pcnn_icp_sums_dev(pcnn_icp_state* st);
 int pcnn_icp_update(pcnn_icp_state* st, pcnn_stream stream);
 int pcnn_icp_finish(pcnn_icp_state* st, pcnn_icp_result* out_host, pcnn_stream stream);
 int pcnn_icp_destroy(pcnn_icp_state* st);
+
+/* Fused form of the same iteration for GPUs that can address each other's memory (NVLink /
+ * NVSwitch on one box): ONE kernel per iteration does accumulate + all-reduce + update.  The
+ * last block of every rank stores its 32 folded sums into a mailbox in every peer's memory
+ * (plain P2P stores, then a system-scope release of a sequence flag), waits for the flags of
+ * all peers in its own mailbox, adds the world's contributions in rank order (so every rank
+ * holds bit-identical sums, whatever the arrival order) and runs the replicated solve.  No
+ * NCCL call, no extra launch, nothing on the host inside the loop.  What replaces which
+ * reference line is unchanged: the sums are those of registration.cpp:788-818 / :964-987
+ * built from ALL pairs.
+ *
+ *     pcnn_icp_peer_export(st, handle, &ptr);      every rank; handle = 64-byte CUDA IPC handle
+ *     <exchange handles (other processes) or ptrs (same process)>
+ *     pcnn_icp_peer_attach(st, rank, world, handles, ptrs);
+ *     max_iter x pcnn_icp_step_peer(st, stream);   every rank, same number of calls
+ *     pcnn_icp_finish(...); pcnn_icp_peer_detach(st); <barrier>; pcnn_icp_destroy(st);
+ *
+ * A peer that does not show up within PCNN_ICP_PEER_TIMEOUT_MS ends the loop on the waiting
+ * rank with status 2 (later steps return at once): the kernel never spins unbounded. */
+#define PCNN_ICP_PEER_HANDLE_BYTES 64
+#define PCNN_ICP_MAX_PEERS 16
+#define PCNN_ICP_PEER_TIMEOUT_MS 4000
+int pcnn_icp_peer_export(pcnn_icp_state* st, void* handle_out /* 64 B, may be NULL */,
+                         void** mailbox_dev_out /* may be NULL */);
+/* handles: world x 64 B from the ranks' pcnn_icp_peer_export (entry `rank` ignored), or NULL when
+ * ptrs (world device pointers valid in THIS process, entry `rank` ignored) is given instead. */
+int pcnn_icp_peer_attach(pcnn_icp_state* st, int rank, int world, const void* handles,
+                         void* const* ptrs);
+int pcnn_icp_step_peer(pcnn_icp_state* st, pcnn_stream stream);
+/* Unmaps the peers' mailboxes; every rank detaches BEFORE any rank destroys its state. */
+int pcnn_icp_peer_detach(pcnn_icp_state* st);
 
 /* Exact float32 1-NN of every query against the index, as the ICP loop uses it
  * (nanoflann.hpp:383-408 key: ((dx*dx)+dy*dy)+dz*dz in float32, dx = q - p; lowest index

@@ -102,6 +102,72 @@ def test_icp_split_phase_equals_fused(pair):
     a.close(); b.close(); ix.close()
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_icp_peer_exchange_one_gpu(pair, mode):
+    """pcnn_icp_step_peer: accumulate + all-reduce through the peers' mailboxes + update in ONE
+    kernel.  Here both "ranks" live on one GPU (two states, two streams, mailboxes attached by
+    pointer); the 2-GPU form over CUDA IPC is tests/test_gpu_multi.py."""
+    import torch
+    src, tar, nrm, T = pair
+    ix = pc.Index(tar)
+    dn = torch.from_numpy(nrm).cuda()
+    one = ix.icp(src, tar_normals=nrm, max_iter=10, mode=mode)
+    # world = 1: the exchange degenerates to the fused kernel, bit for bit
+    st = pc.IcpState(ix, torch.from_numpy(src).cuda(), tar_normals=dn, max_iter=10, mode=mode)
+    _, ptr = st.export_mailbox()
+    st.attach_local_peers(0, [ptr])
+    for _ in range(10):
+        st.step_peer()
+    solo = st.finish()
+    st.close()
+    assert np.array_equal(solo["T"], one["T"]) and solo["pairs"] == one["pairs"] and solo["status"] == 0
+    # world = 3, uneven shards (one of them empty)
+    cuts = [0, len(src) // 3, len(src) // 3, len(src)]
+    states = [pc.IcpState(ix, torch.from_numpy(src[cuts[r]:cuts[r + 1]]).cuda(), tar_normals=dn, max_iter=10,
+                          mode=mode, src_index_base=cuts[r]) for r in range(3)]
+    ptrs = [s.export_mailbox()[1] for s in states]
+    streams = [torch.cuda.Stream() for _ in states]
+    torch.cuda.synchronize()
+    for r, s in enumerate(states):
+        s.attach_local_peers(r, ptrs)
+    for _ in range(10):
+        for s, stream in zip(states, streams):
+            with torch.cuda.stream(stream):
+                s.step_peer()
+    res = []
+    for s, stream in zip(states, streams):
+        with torch.cuda.stream(stream):
+            res.append(s.finish())
+    for s in states:
+        s.detach_peers()
+    for s in states:
+        s.close()
+    for r in res:
+        assert r["status"] == 0 and r["iters"] == 10 and r["pairs"] == one["pairs"]
+        assert np.array_equal(r["T"], res[0]["T"])  # rank-ordered sums: identical bits on every rank
+    assert parity.rot_err(res[0]["T"], one["T"]) < 1e-6 and parity.trans_err(res[0]["T"], one["T"]) < 1e-6
+    ix.close()
+
+
+def test_icp_peer_timeout_is_bounded(pair):
+    """A peer that never steps: the waiting rank gives up after PCNN_ICP_PEER_TIMEOUT_MS with
+    status 2 instead of spinning; later steps return at once."""
+    import time
+    import torch
+    src, tar, nrm, T = pair
+    ix = pc.Index(tar)
+    a = pc.IcpState(ix, torch.from_numpy(src[:1000]).cuda(), max_iter=5, mode=0)
+    b = pc.IcpState(ix, torch.from_numpy(src[1000:2000]).cuda(), max_iter=5, mode=0, src_index_base=1000)
+    ptrs = [a.export_mailbox()[1], b.export_mailbox()[1]]
+    a.attach_local_peers(0, ptrs)
+    t0 = time.time()
+    for _ in range(5):
+        a.step_peer()
+    r = a.finish()
+    assert r["status"] == 2 and r["iters"] == 0 and time.time() - t0 < 8.0
+    a.detach_peers(); a.close(); b.close(); ix.close()
+
+
 # ---------------------------------------------------------------- full-size properties
 @pytest.fixture(scope="module")
 def big():

@@ -21,7 +21,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libpcnn.so")
+# PCNN_LIB: developer override to load another BUILD of the same library (tools/tune_*.py)
+_LIB_PATH = os.environ.get("PCNN_LIB") or os.path.join(_HERE, "libpcnn.so")
 _lib = None
 
 KDTREE, OCTREE = 0, 1
@@ -51,7 +52,7 @@ class IcpParams(C.Structure):
 class IcpResult(C.Structure):
     _fields_ = [("T", C.c_float * 16), ("iters", C.c_int32), ("converged", C.c_int32),
                 ("status", C.c_int32), ("last_loss", C.c_float), ("last_pairs", C.c_int64),
-                ("loop_ms", C.c_float), ("reserved", C.c_int32)]
+                ("loop_ms", C.c_float), ("last_searches", C.c_int32)]
 
 
 class IssParams(C.Structure):

@@ -28,6 +28,9 @@ struct pcnn_icp_state {
     float4* cur = nullptr;       // source cloud, current pose, Morton order, .w = global source index
     float4* nrm = nullptr;       // target normals in the index's Morton order (mode 1)
     int* prev = nullptr;         // per source point: Morton position of its last correspondence (-1 = none)
+    float4* cert = nullptr;      // per source point: where it was last searched (.xyz) and the certificate radius (.w)
+    int use_cert = 1;
+    float gapk = 4.0f, move_frac = 0.03f;
     double* partials = nullptr;  // [nblocks][32]
     struct Dev* dev = nullptr;   // device-resident loop state
     int nblocks = 0;
@@ -67,6 +70,9 @@ struct Dev {
     long long last_pairs;
     unsigned block_counter;
     unsigned long long peer_seq;  // iterations exchanged so far (identical on every rank)
+    unsigned long long walked;    // searches run so far (the rest were certified); PCNN_ICP_STATS prints it
+    unsigned long long walked_mark;
+    int last_searches;            // searches of the last executed iteration
 };
 
 // One per rank, in that rank's memory; peers store into it.  Two slots: a rank can be at most
@@ -121,6 +127,8 @@ __device__ bool chol6_dev(const double* N, const double* g, double* x) {
 // Runs in one thread; every rank computes the identical result from identical sums.
 __device__ void icp_update_dev(Dev* st, int mode, float loss_epsilon) {
     if (st->done) return;
+    st->last_searches = (int)(st->walked - st->walked_mark);
+    st->walked_mark = st->walked;
     const double* S = st->sums;
     const double M = S[28];
     float R[9], t[3];
@@ -264,18 +272,160 @@ __device__ double peer_exchange(const PeerView& pv, Dev* st, int col, double r) 
 // KIND 0 = split phase (sums only), 1 = fused update, 2 = fused peer all-reduce + update.
 // Blocks walk the source cloud with a grid stride (whole warps: tail lanes shadow the last
 // point and contribute nothing), each thread keeps its sums in registers across its points.
+// Register budget, measured on B200 (1M source x 1M target, us per iteration, p2plane / p2p,
+// identical pose bits): search and sums in one loop with unbounded registers (112-135) 782 / 663;
+// the same at 8 blocks/SM (64 registers) 536 / 523; search first, sums in a second pass over the
+// block's points, 8 blocks/SM 510 / 502.  The walk is latency-bound: resident warps matter more
+// than the 16-190 B of spills, and in two passes the 16 / 29 double sums are not live during it.
+#ifndef PCNN_ICP_MINBLOCKS
+#define PCNN_ICP_MINBLOCKS 8
+#endif
+constexpr int ICP_J = 4;  // slices of 128 source points a block takes together
+
+// Correspondence certificate.  A search at position c found the nearest target point x1 and a
+// floor key2 under the keys of all others (Best2f).  With u = 2^-24 the float32 key of nanoflann is
+// K(p, x) = D(p, x)^2 (1 + t), |t| <= 5u, D the true distance.  So D(c, x) >= sqrt(key2)(1 - 3u)
+// for x != x1, and after the source point has moved to p: D(p, x) >= sqrt(key2)(1 - 3u) - |p - c|.
+// If that exceeds sqrt(K(p, x1))(1 + 3u), every other point has a strictly larger KEY than x1 at p:
+// x1 is still what the search would return, ties included, and the search is skipped.  The
+// margins below (1e-5 relative, directed rounding) cover the u terms a hundred times over.
+// The floor is chased only as far as the point is expected to travel (Best2f::gap): ICP_GAPK times
+// what this iteration's T_delta moved it, and not at all while that exceeds a quarter of the
+// cloud's mean 8-point-group extent -- the spacing of the target bounds d2 - d1, so a certificate
+// against a larger motion would cost a wide search and fail anyway.
+constexpr float ICP_GAPK = 4.0f, ICP_MOVE_MAX = 0.03f;
+__device__ __forceinline__ float cert_radius(float floor_key) { return __fmul_rd(__fsqrt_rd(floor_key), 0.99999f); }
+__device__ __forceinline__ bool cert_holds(const float4& p, const float4& c, float k1) {
+    if (!(c.w > 0.f)) return false;
+    const float dx = fabsf(p.x - c.x), dy = fabsf(p.y - c.y), dz = fabsf(p.z - c.z);
+    const float m2 = __fadd_ru(__fadd_ru(__fmul_ru(dx, dx), __fmul_ru(dy, dy)), __fmul_ru(dz, dz));
+    const float s = __fmul_ru(__fadd_ru(__fsqrt_ru(k1), __fsqrt_ru(m2)), 1.00001f);
+    return s < c.w;
+}
+
+// Kernel 1 of an iteration: pending T_delta, certificates, searches.  64 registers, 8 blocks per SM.
+__global__ void __launch_bounds__(ICP_THREADS, PCNN_ICP_MINBLOCKS)
+icp_search_kernel(IndexView iv, float4* cur, int* prev, float4* cert, int n_src, int use_cert, float gapk,
+                  float move_frac, float max_corres_dist, Dev* __restrict__ st) {
+    __shared__ int s_qg[LS_QDEPTH][ICP_THREADS];
+    __shared__ float s_ql[LS_QDEPTH][ICP_THREADS];
+    __shared__ unsigned short s_list[ICP_J * ICP_THREADS];  // (slice of the group, thread) of a point to search
+    __shared__ float s_move[ICP_J * ICP_THREADS];           // how far T_delta moved the point
+    __shared__ int s_nwalk;
+    if (st->done) return;  // uniform: loop already ended (converged / failed)
+    const float move_max = move_frac * __ldg(iv.cube + 8);
+    const float gap_min = 1e-3f * __ldg(iv.cube + 8) + 1e-6f;  // rides out the last-bit jitter of a converged pose
+    const bool first_done = st->iters > 0 || st->unchanged > 0 || st->last_pairs > 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float Rd[9], td[3];
+#pragma unroll
+    for (int i = 0; i < 9; i++) Rd[i] = st->Rd[i];
+#pragma unroll
+    for (int i = 0; i < 3; i++) td[i] = st->td[i];
+    const unsigned full = 0xffffffffu;
+    constexpr int J = ICP_J;
+    const int nsl = (n_src + ICP_THREADS - 1) / ICP_THREADS;  // slices of 128 consecutive (Morton-ordered) points
+    const int G = (int)gridDim.x;
+    // A block owns the slices blockIdx.x, + G, + 2G, ... (spread over the cloud: dense
+    // regions walk longer, contiguous chunks would unbalance the blocks) and takes them J at a time:
+    // apply the pending T_delta, test every point's certificate -- the loads of the J slices issued
+    // together, a converged iteration is nothing but these dependent loads -- and collect the
+    // points that need a search; then the block's warps search the collected points 32 at a time,
+    // so a nearly converged iteration runs a few dense warps instead of every warp for its one or
+    // two uncertified lanes.  The sums are not live here: the walk gets the registers.
+    for (int s0 = blockIdx.x; s0 < nsl; s0 += J * G) {
+        if (threadIdx.x == 0) s_nwalk = 0;
+        __syncthreads();
+        int tj[J], ppj[J];
+        float4 pj[J], cj[J];
+#pragma unroll
+        for (int j = 0; j < J; j++) {
+            const int t = (s0 + j * G) * ICP_THREADS + threadIdx.x;
+            tj[j] = (s0 + j * G < nsl && t < n_src) ? t : -1;
+            if (tj[j] >= 0) pj[j] = cur[tj[j]];
+        }
+#pragma unroll
+        for (int j = 0; j < J; j++) {
+            ppj[j] = -1;
+            if (tj[j] >= 0) {
+                float4 p = pj[j];
+                const float ox = p.x, oy = p.y, oz = p.z;
+                xform(Rd, td, p.x, p.y, p.z);  // pending T_delta of the previous iteration
+                cur[tj[j]] = p;
+                pj[j] = p;
+                s_move[j * ICP_THREADS + threadIdx.x] =
+                    fmaxf(fmaxf(fabsf(p.x - ox), fabsf(p.y - oy)), fabsf(p.z - oz)) * 1.7320509f;
+                if (use_cert) {
+                    ppj[j] = prev[tj[j]];
+                    cj[j] = cert[tj[j]];
+                }
+            }
+        }
+        float4 qj[J];
+#pragma unroll
+        for (int j = 0; j < J; j++)
+            if (ppj[j] >= 0) qj[j] = __ldg(iv.pts + ppj[j]);
+#pragma unroll
+        for (int j = 0; j < J; j++) {
+            bool need = tj[j] >= 0;
+            if (need && use_cert) {
+                // no correspondence (pp < 0): the certificate says nothing lies within c.w of c; with
+                // the gate as the key it reads "still nothing within the gate"
+                const float k1 = ppj[j] >= 0 ? key32(qj[j].x, qj[j].y, qj[j].z, pj[j].x, pj[j].y, pj[j].z) : max_corres_dist;
+                need = !cert_holds(pj[j], cj[j], k1);
+            }
+            const unsigned m = __ballot_sync(full, need);
+            int at = 0;
+            if (lane == 0 && m) at = atomicAdd(&s_nwalk, __popc(m));
+            at = __shfl_sync(full, at, 0);
+            if (need) s_list[at + __popc(m & ((1u << lane) - 1u))] = (unsigned short)(j * ICP_THREADS + threadIdx.x);
+        }
+        __syncthreads();
+        const int nw = s_nwalk;
+        if (threadIdx.x == 0 && nw) atomicAdd(&st->walked, (unsigned long long)nw);
+        for (int b = warp << 5; b < nw; b += ICP_THREADS) {  // whole warps; tail lanes shadow the last entry
+            const int i = b + lane;
+            const bool live = i < nw;
+            const int e = s_list[live ? i : nw - 1];
+            const int t = (s0 + (e / ICP_THREADS) * G) * ICP_THREADS + (e % ICP_THREADS);
+            const float4 p = cur[t];
+            const int pp = prev[t];
+            Best2f best;
+            const float moved = s_move[e];
+            // a point searched for the first time (iteration 0 of a state) has not moved yet: no certificate
+            best.gap = (use_cert && first_done && moved < move_max) ? gapk * moved + gap_min : -1.f;
+            // the gate doubles as the search bound: a neighbour at or beyond it is dropped anyway.  With a
+            // certificate in view the bound reaches `gap` beyond the gate, so that "nothing within the
+            // gate" can be certified too (those searches are the widest of all: a 1 m ball)
+            float bound = max_corres_dist;
+            if (best.gap >= 0.f) {
+                const float r = __fadd_ru(__fmul_ru(__fsqrt_ru(max_corres_dist), 1.0001f), best.gap);  // as Best2f::reach
+                bound = __fmul_ru(r, r);
+            }
+            nn1_lockstep<ICP_THREADS>(iv, p.x, p.y, p.z, pp >= 0 ? (pp >> PCNN_GROUP_LOG) : -1, bound, best,
+                                      s_qg, s_ql, threadIdx.x);
+            if (live) {
+                prev[t] = best.pos;
+                cert[t] = make_float4(p.x, p.y, p.z, best.gap >= 0.f ? cert_radius(best.lim) : -1.f);
+            }
+        }
+        __syncthreads();  // s_list is reused
+    }
+}
+
+// Kernel 2 of an iteration: the pairs' terms, their reduction, and (KIND) the solve / the exchange.
+// Its own register budget: 16 / 29 double sums per thread next to J slices of loads in flight.
 template <int MODE, int KIND>
-__global__ void __launch_bounds__(ICP_THREADS)
-icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __restrict__ nrm,
-                      int* __restrict__ prev, int n_src, float max_corres_dist, float loss_epsilon,
-                      Dev* __restrict__ st, double* __restrict__ partials, const PeerView pv) {
+__global__ void __launch_bounds__(ICP_THREADS, 4)
+icp_accumulate_kernel(IndexView iv, const float4* cur, const float4* __restrict__ nrm, const int* prev, int n_src,
+                      float max_corres_dist, float loss_epsilon, Dev* __restrict__ st, double* __restrict__ partials,
+                      const PeerView pv) {
     constexpr bool FUSED = KIND != 0;
     constexpr int NT = MODE == 0 ? 16 : 29;
+    constexpr int J = ICP_J;
     __shared__ double s_part[ICP_THREADS / 32][ICP_NS];
     __shared__ long long s_last[ICP_THREADS / 32];
     __shared__ bool s_is_last;
-    __shared__ int s_qg[LS_QDEPTH][ICP_THREADS];
-    __shared__ float s_ql[LS_QDEPTH][ICP_THREADS];
     if (st->done) return;  // uniform: loop already ended (converged / failed)
 #ifdef PCNN_ICP_TIMING
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -293,26 +443,37 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
 #pragma unroll
     for (int i = 0; i < NT; i++) v[i] = 0.0;
     long long last = -1;
-    float Rd[9], td[3];
+    const int nsl = (n_src + ICP_THREADS - 1) / ICP_THREADS;
+    const int G = (int)gridDim.x;
+    // points assigned to threads in a fixed pattern (the sums do not depend on which lane searched
+    // what): the slices blockIdx.x, + G, ... of the search kernel, J at a time so their loads overlap
+    for (int s0 = blockIdx.x; s0 < nsl; s0 += J * G) {
+        float4 pj[J], qj[J], nj[J];
+        int posj[J];
 #pragma unroll
-    for (int i = 0; i < 9; i++) Rd[i] = st->Rd[i];
+        for (int j = 0; j < J; j++) {
+            const int t = (s0 + j * G) * ICP_THREADS + threadIdx.x;
+            posj[j] = -1;
+            if (s0 + j * G < nsl && t < n_src) {
+                pj[j] = cur[t];
+                posj[j] = prev[t];
+            }
+        }
 #pragma unroll
-    for (int i = 0; i < 3; i++) td[i] = st->td[i];
-    for (int base = blockIdx.x * ICP_THREADS; base < n_src; base += gridDim.x * ICP_THREADS) {
-        const int t = base + threadIdx.x;
-        const bool live = t < n_src;
-        const int tt = live ? t : n_src - 1;
-        float4 p = cur[tt];
-        xform(Rd, td, p.x, p.y, p.z);  // pending T_delta of the previous iteration
-        if (live) cur[t] = p;
+        for (int j = 0; j < J; j++)
+            if (posj[j] >= 0) {
+                qj[j] = __ldg(iv.pts + posj[j]);
+                if (MODE == 1) nj[j] = __ldg(nrm + posj[j]);
+            }
+#pragma unroll
+        for (int j = 0; j < J; j++) {
+        const bool live = posj[j] >= 0;
+        const float4 p = pj[j], qpt = qj[j];
         Best1f best;
-        const int pp = prev[tt];
-        // the gate doubles as the search bound: a neighbour at or beyond it is dropped anyway
-        nn1_lockstep<ICP_THREADS>(iv, p.x, p.y, p.z, pp >= 0 ? (pp >> PCNN_GROUP_LOG) : -1, max_corres_dist, best,
-                                  s_qg, s_ql, threadIdx.x);
-        if (live) prev[t] = best.pos;
+        best.init();
+        best.pos = posj[j];
+        if (live) best.key = key32(qpt.x, qpt.y, qpt.z, p.x, p.y, p.z);  // the key the walk found, same arithmetic
         if (live && best.pos >= 0 && best.key < max_corres_dist) {  // gate on the SQUARED distance (:783, :936)
-            const float4 qpt = __ldg(iv.pts + best.pos);
             if (MODE == 0) {
                 v[0] += p.x; v[1] += p.y; v[2] += p.z;
                 v[3] += qpt.x; v[4] += qpt.y; v[5] += qpt.z;
@@ -324,7 +485,7 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
                     ((long long)__float_as_int(p.w) << 32) | (long long)(unsigned)__float_as_int(best.key);
                 last = cand > last ? cand : last;
             } else {
-                const float4 nn = __ldg(nrm + best.pos);
+                const float4 nn = nj[j];
                 // row of A and b in float32 exactly as written at registration.cpp:808-814
                 float a[6];
                 a[0] = fadd(fmul(nn.z, p.y), -fmul(nn.y, p.z));
@@ -345,6 +506,7 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
                 v[27] += (double)b * (double)b;
                 v[28] += 1.0;
             }
+        }
         }
     }
 #pragma unroll
@@ -391,7 +553,7 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
         const int col = threadIdx.x & 31, part = threadIdx.x >> 5;  // 4 row-strided partial sums per column
         // fixed order whatever the timing: 8 interleaved accumulators per (column, part), then a
         // fixed tree; the loads of one batch are independent so they overlap
-        constexpr int P4 = ICP_THREADS / 32, UN = 8;
+        constexpr int P4 = ICP_THREADS / 32, UN = 16;
         double acc[UN];
         long long mm[UN];
 #pragma unroll
@@ -410,7 +572,11 @@ icp_accumulate_kernel(IndexView iv, float4* __restrict__ cur, const float4* __re
                 else acc[u] += x[u];
             }
         }
-        double s = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+#pragma unroll
+        for (int w = UN / 2; w > 0; w >>= 1)  // fixed tree
+#pragma unroll
+            for (int u = 0; u < w; u++) acc[u] += acc[u + w];
+        const double s = acc[0];
         long long m = -1;
 #pragma unroll
         for (int u = 0; u < UN; u++) m = mm[u] > m ? mm[u] : m;
@@ -491,6 +657,7 @@ __global__ void icp_state_init_kernel(Dev* st, const float* __restrict__ T0) {
         st->iters = 0; st->converged = 0; st->status = 0; st->done = 0; st->unchanged = 0;
         st->last_loss = 0.f; st->loss = 0.f; st->last_pairs = 0; st->block_counter = 0;
         st->peer_seq = 0;
+        st->walked = 0; st->walked_mark = 0; st->last_searches = 0;
     }
 }
 
@@ -540,7 +707,7 @@ static void icp_free(pcnn_icp_state* st) {
     if (!st) return;
     icp_peer_detach(st);
     if (st->box) cudaFree(st->box);
-    void* ptrs[5] = {st->cur, st->nrm, st->prev, st->partials, st->dev};
+    void* ptrs[6] = {st->cur, st->nrm, st->prev, st->partials, st->dev, st->cert};
     for (void* p : ptrs)
         if (p) cudaFreeAsync(p, st->mem_stream);
     delete st;
@@ -557,6 +724,8 @@ static int icp_launch_accumulate(pcnn_icp_state* st, int kind, cudaStream_t s) {
         for (int p = 0; p < st->world; p++) pv.box[p] = st->peer[p];
         pv.rank = st->rank; pv.world = st->world;
     }
+    icp_search_kernel<<<st->nblocks, ICP_THREADS, 0, s>>>(ix->view, st->cur, st->prev, st->cert, n, st->use_cert, st->gapk,
+                                                          st->move_frac, st->prm.max_corres_dist, st->dev);
 #define PCNN_ICP_LAUNCH(MODE, KIND)                                                              \
     icp_accumulate_kernel<MODE, KIND><<<st->nblocks, ICP_THREADS, 0, s>>>(                       \
         ix->view, st->cur, st->nrm, st->prev, n, st->prm.max_corres_dist, st->prm.loss_epsilon, st->dev, st->partials, pv)
@@ -596,9 +765,21 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
     if (!st) { set_error("pcnn_icp_create: host allocation failed"); return PCNN_ERR_NOMEM; }
     st->target = target; st->device = target->device; st->n_src = n_src; st->prm = *params;
     const int n = (int)n_src;
-    st->nblocks = (n + ICP_THREADS - 1) / ICP_THREADS;
-    if (st->nblocks < 1) st->nblocks = 1;
-    if (st->nblocks > 148 * 8) st->nblocks = 148 * 8;  // grid stride beyond 8 resident blocks per SM
+    {
+        // one block per 128-point slice up to what is resident at once (blocks per SM from the
+        // occupancy calculator); beyond that the grid strides over the slices
+        int per_sm = 0, sms = 148;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)icp_search_kernel, ICP_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, st->device);
+        if (per_sm > 8) per_sm = 8;
+        if (const char* e = getenv("PCNN_ICP_CERT")) st->use_cert = atoi(e) != 0;
+        st->gapk = ICP_GAPK; st->move_frac = ICP_MOVE_MAX;
+        if (const char* e = getenv("PCNN_ICP_GAPK")) st->gapk = (float)atof(e);
+        if (const char* e = getenv("PCNN_ICP_MOVE")) st->move_frac = (float)atof(e);
+        st->nblocks = (n + ICP_THREADS - 1) / ICP_THREADS;
+        if (st->nblocks < 1) st->nblocks = 1;
+        if (st->nblocks > sms * per_sm) st->nblocks = sms * per_sm;
+    }
     st->mem_stream = s;
     cudaMemPool_t pool = lib_pool();
     auto palloc = [&](auto** out, size_t bytes) -> cudaError_t {
@@ -609,6 +790,7 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
     };
     cudaError_t e = palloc(&st->cur, sizeof(float4) * (size_t)(n + 1));
     if (e == cudaSuccess) e = palloc(&st->prev, sizeof(int) * (size_t)(n + 1));
+    if (e == cudaSuccess) e = palloc(&st->cert, sizeof(float4) * (size_t)(n + 1));
     if (e == cudaSuccess) e = palloc(&st->partials, sizeof(double) * ICP_NS * (size_t)st->nblocks);
     if (e == cudaSuccess) e = palloc(&st->dev, sizeof(Dev));
     if (e == cudaSuccess && params->mode == 1) e = palloc(&st->nrm, sizeof(float4) * (size_t)(target->n + 1));
@@ -631,6 +813,7 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
         } else {
             icp_state_init_kernel<<<1, 32, 0, s>>>(st->dev, T0);
             e = cudaMemsetAsync(st->prev, 0xff, sizeof(int) * (size_t)(n + 1), s);  // -1: no correspondence yet
+            if (e == cudaSuccess) e = cudaMemsetAsync(st->cert, 0xff, sizeof(float4) * (size_t)(n + 1), s);  // NaN: no certificate
             if (n > 0) {
                 icp_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(src_dev, n, stride, (long long)src_index_base, T0, tmp);
                 unsigned* perm = nullptr;
@@ -756,6 +939,10 @@ int pcnn_icp_finish(pcnn_icp_state* st, pcnn_icp_result* out_host, pcnn_stream s
     Dev h;
     PCNN_CUDA(cudaMemcpyAsync(&h, st->dev, sizeof(Dev), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     PCNN_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    if (getenv("PCNN_ICP_STATS"))
+        fprintf(stderr, "pcnn_icp: %llu searches for %lld points x %d iterations (%.1f %% certified)\n", h.walked,
+                (long long)st->n_src, h.iters,
+                h.iters > 0 && st->n_src > 0 ? 100.0 - 100.0 * (double)h.walked / ((double)st->n_src * h.iters) : 0.0);
     std::memcpy(out_host->T, h.T, sizeof(h.T));
     out_host->iters = h.iters;
     out_host->converged = h.converged;
@@ -763,7 +950,7 @@ int pcnn_icp_finish(pcnn_icp_state* st, pcnn_icp_result* out_host, pcnn_stream s
     out_host->last_loss = h.last_loss;
     out_host->last_pairs = h.last_pairs;
     out_host->loop_ms = 0.f;
-    out_host->reserved = 0;
+    out_host->last_searches = h.last_searches;
     return PCNN_OK;
 }
 

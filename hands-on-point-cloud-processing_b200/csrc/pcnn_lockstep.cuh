@@ -20,8 +20,9 @@ namespace pcnn {
 constexpr int LS_QDEPTH = 4;  // queued groups per lane
 constexpr int LS_WALK = 8;    // steps per round
 
+template <class BEST>
 __device__ __forceinline__ void nn1_scan_group(const IndexView& iv, int g, float qx, float qy, float qz,
-                                               Best1f& best) {
+                                               BEST& best) {
     const int first = g << PCNN_GROUP_LOG;
     const int cnt = (iv.n - first) < PCNN_GROUP ? (iv.n - first) : PCNN_GROUP;
 #pragma unroll
@@ -30,34 +31,37 @@ __device__ __forceinline__ void nn1_scan_group(const IndexView& iv, int g, float
             const float4 p = __ldg(iv.pts + first + j);
             const float d = key32(p.x, p.y, p.z, qx, qy, qz);
             const int id = __float_as_int(p.w);
-            if (kless32(d, id, best.key, best.idx)) { best.key = d; best.idx = id; best.pos = first + j; }
+            best.offer(d, id, first + j);
         }
     }
 }
 
 // s_qg / s_ql: shared-memory queues [LS_QDEPTH][THREADS], column `tid` belongs to this lane.
-template <int THREADS>
+template <int THREADS, class BEST>
 __device__ __forceinline__ void nn1_lockstep(const IndexView& iv, float qx, float qy, float qz, int seed_group,
-                                             float bound, Best1f& best, int (*s_qg)[THREADS],
+                                             float bound, BEST& best, int (*s_qg)[THREADS],
                                              float (*s_ql)[THREADS], int tid) {
     const unsigned full = 0xffffffffu;
     const float INFf = __int_as_float(0x7f800000);
-    best.init();
     // `bound`: the caller only wants a neighbour with key < bound (ICP's gate on the squared
     // distance, registration.cpp:783 / :936); farther ones may be reported as "none" (pos = -1)
-    best.key = bound;
+    best.start(bound);
     if (iv.n <= 0) return;
     const unsigned long long qcode = morton63(qx, qy, qz, iv.cube, iv.cube[3]);
     if (seed_group < 0 || seed_group >= iv.n0) seed_group = home_group(iv, qcode);
     nn1_scan_group(iv, seed_group, qx, qy, qz, best);
     const int top = iv.nlev - 1;
-    // start as low in the tree as the seed bound allows; with a warm start that is a few levels
-    int l = walk_start_level(iv, seed_group, qx, qy, qz, best.key);
+    // start as low in the tree as the seed bound allows; with a warm start that is a few levels.
+    // (Measured alternative: start AT the seed group with the sibling subtrees of its ancestors tested
+    // up front by independent loads and only climb.  Slower both with many searches in flight, 570 vs
+    // 500 us per 1M-point ICP iteration, and with a few hundred, 148 vs 122 us: every sibling that
+    // passes costs a pop and a re-test, where the descent prunes most of them on the way down.)
+    int l = walk_start_level(iv, seed_group, qx, qy, qz, best.bound());
     int n = seed_group >> l;
     unsigned pending = 0;
     int mode = 0;  // 0 = examine the children of (l, n), 1 = backtrack
-    bool done = top == 0;
     int cnt = 0;
+    bool done = top == 0;
     while (true) {
 #pragma unroll 1
         for (int s = 0; s < LS_WALK; s++) {
@@ -98,8 +102,8 @@ __device__ __forceinline__ void nn1_lockstep(const IndexView& iv, float qx, floa
                         const float lbn = first1 ? lbB : lbA, lbf = first1 ? lbA : lbB;
                         const int near = P + (first1 ? 1 : 0);
                         // strict test: a box at exactly the best key may hold a lower index
-                        const bool passN = !(lbn > best.key);
-                        const bool passF = !(lbf > best.key) && lbf < INFf;
+                        const bool passN = !(lbn > best.bound());
+                        const bool passF = !(lbf > best.bound()) && lbf < INFf;
                         if (L == 0) {
                             if (passN && near != seed_group) { s_qg[cnt][tid] = near; s_ql[cnt][tid] = lbn; cnt++; }
                             if (passF && (near ^ 1) != seed_group) { s_qg[cnt][tid] = near ^ 1; s_ql[cnt][tid] = lbf; cnt++; }
@@ -113,7 +117,7 @@ __device__ __forceinline__ void nn1_lockstep(const IndexView& iv, float qx, floa
                         }
                     } else {
                         const float lbv = (far & 1) ? lbB : lbA;
-                        if (!(lbv > best.key)) mode = 0;
+                        if (!(lbv > best.bound())) mode = 0;
                     }
                 }
             }
@@ -121,7 +125,7 @@ __device__ __forceinline__ void nn1_lockstep(const IndexView& iv, float qx, floa
         {
             const int maxc = __reduce_max_sync(full, cnt);
             for (int r = 0; r < maxc; r++)
-                if (r < cnt && !(s_ql[r][tid] > best.key)) nn1_scan_group(iv, s_qg[r][tid], qx, qy, qz, best);
+                if (r < cnt && !(s_ql[r][tid] > best.bound())) nn1_scan_group(iv, s_qg[r][tid], qx, qy, qz, best);
             cnt = 0;
         }
         if (!__any_sync(full, !done)) break;

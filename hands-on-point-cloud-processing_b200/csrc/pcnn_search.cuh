@@ -87,6 +87,44 @@ struct Best1f {
     int idx;  // original index
     int pos;  // position in Morton order (lets callers fetch per-point attributes)
     PCNN_HD void init() { key = i2f(0x7f800000); idx = 0x7fffffff; pos = -1; }
+    PCNN_HD void start(float b) { init(); key = b; }
+    PCNN_HD float bound() const { return key; }
+    PCNN_HD void offer(float d, int id, int p) {
+        if (kless32(d, id, key, idx)) { key = d; idx = id; pos = p; }
+    }
+};
+// The nearest point and a FLOOR under everybody else: once the search has ended, every point
+// other than `pos` has key >= lim (examined ones by comparison, pruned ones because their box
+// bound exceeded the pruning key, which only falls).  ICP turns lim into a certificate that lets
+// later iterations keep the correspondence without searching (pcnn_icp.cu).  The floor is only
+// chased up to (sqrt(key) + gap)^2: a caller that expects its query to move by less than `gap`
+// needs no more, and the walk then costs little more than a plain 1-NN walk (gap < 0: exactly
+// that, lim == key, no certificate).
+struct Best2f {
+    float key;
+    int idx;
+    int pos;
+    float lim;  // pruning key = min(second smallest key seen, (sqrt(key)(1 + 1e-4) + gap)^2)
+    float gap;
+    PCNN_HD void init() { key = i2f(0x7f800000); idx = 0x7fffffff; pos = -1; lim = key; gap = -1.f; }
+    PCNN_HD void start(float b) { key = b; idx = 0x7fffffff; pos = -1; lim = b; }
+    PCNN_HD float bound() const { return lim; }
+#if defined(__CUDACC__)
+    __device__ __forceinline__ float reach(float k) const {
+        if (gap < 0.f) return k;
+        const float r = __fadd_ru(__fmul_ru(__fsqrt_ru(k), 1.0001f), gap);
+        return __fmul_ru(r, r);
+    }
+    __device__ __forceinline__ void offer(float d, int id, int p) {
+        if (kless32(d, id, key, idx)) {
+            const float second = key;  // the displaced best is now the nearest of the others
+            key = d; idx = id; pos = p;
+            lim = fminf(fminf(lim, second), reach(d));
+        } else if (d < lim) {
+            lim = d;
+        }
+    }
+#endif
 };
 
 // index of the base group whose code range holds qc: last g with gcode[g] <= qc (or 0)

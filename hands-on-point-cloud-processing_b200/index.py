@@ -218,7 +218,7 @@ class Index:
 def _icp_dict(res):
     return {"T": np.array(list(res.T), np.float32).reshape(4, 4), "iters": res.iters,
             "converged": res.converged, "status": res.status, "loss": res.last_loss,
-            "pairs": res.last_pairs, "loop_ms": res.loop_ms}
+            "pairs": res.last_pairs, "loop_ms": res.loop_ms, "searches": res.last_searches}
 
 
 class IcpState:

@@ -193,7 +193,8 @@ typedef struct {
     int64_t last_pairs; /* correspondences kept in the last executed iteration */
     float loop_ms;      /* pcnn_icp / pcnn_icp_host: device time of the iteration loop alone
                            (CUDA events on the stream); 0 from pcnn_icp_finish */
-    int32_t reserved;
+    int32_t last_searches; /* source points searched in the last executed iteration; the others kept
+                              their correspondence under a certificate (same result, no search) */
 } pcnn_icp_result;
 
 /* Whole loop on one GPU: no host synchronisation per iteration; one at the end to return

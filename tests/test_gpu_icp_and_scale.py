@@ -103,6 +103,34 @@ def test_icp_split_phase_equals_fused(pair):
 
 
 @pytest.mark.parametrize("mode", [0, 1])
+def test_icp_certificates_change_nothing_but_the_work(pair, mode, monkeypatch):
+    """Correspondence certificates (pcnn_icp.cu: a point whose nearest neighbour provably cannot
+    have changed is not searched again) must leave every bit of the result alone: same pose, pairs
+    and loss with them switched off, and the number of searches per iteration must fall once the
+    pose settles."""
+    import torch
+    src, tar, nrm, T = pair
+    ix = pc.Index(tar)
+    dn, ds = torch.from_numpy(nrm).cuda(), torch.from_numpy(src).cuda()
+    on = ix.icp(ds, tar_normals=dn, max_iter=40, mode=mode)
+    monkeypatch.setenv("PCNN_ICP_CERT", "0")     # developer switch, read when the state is created
+    off = ix.icp(ds, tar_normals=dn, max_iter=40, mode=mode)
+    monkeypatch.delenv("PCNN_ICP_CERT")
+    assert off["searches"] == len(src)
+    assert np.array_equal(on["T"], off["T"]) and on["pairs"] == off["pairs"] and on["loss"] == off["loss"]
+    assert on["iters"] == off["iters"] == 40
+    st = pc.IcpState(ix, ds, tar_normals=dn, max_iter=40, mode=mode)
+    counts = []
+    for _ in range(40):
+        st.accumulate()
+        st.update()
+        counts.append(st.finish()["searches"])
+    st.close()
+    assert counts[0] == len(src) and counts[-1] < len(src) // (20 if mode == 1 else 2), counts
+    ix.close()
+
+
+@pytest.mark.parametrize("mode", [0, 1])
 def test_icp_peer_exchange_one_gpu(pair, mode):
     """pcnn_icp_step_peer: accumulate + all-reduce through the peers' mailboxes + update in ONE
     kernel.  Here both "ranks" live on one GPU (two states, two streams, mailboxes attached by

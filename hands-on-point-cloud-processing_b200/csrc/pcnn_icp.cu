@@ -29,6 +29,7 @@ struct pcnn_icp_state {
     float4* nrm = nullptr;       // target normals in the index's Morton order (mode 1)
     int* prev = nullptr;         // per source point: Morton position of its last correspondence (-1 = none)
     float4* cert = nullptr;      // per source point: where it was last searched (.xyz) and the certificate radius (.w)
+    int* prev2 = nullptr;        // per source point: the runner-up of that search if it matters to the certificate, else -1
     int use_cert = 1;
     float gapk = 4.0f, move_frac = 0.03f;
     double* partials = nullptr;  // [nblocks][32]
@@ -305,7 +306,7 @@ __device__ __forceinline__ bool cert_holds(const float4& p, const float4& c, flo
 
 // Kernel 1 of an iteration: pending T_delta, certificates, searches.  64 registers, 8 blocks per SM.
 __global__ void __launch_bounds__(ICP_THREADS, PCNN_ICP_MINBLOCKS)
-icp_search_kernel(IndexView iv, float4* cur, int* prev, float4* cert, int n_src, int use_cert, float gapk,
+icp_search_kernel(IndexView iv, float4* cur, int* prev, int* prev2, float4* cert, int n_src, int use_cert, float gapk,
                   float move_frac, float max_corres_dist, Dev* __restrict__ st) {
     __shared__ int s_qg[LS_QDEPTH][ICP_THREADS];
     __shared__ float s_ql[LS_QDEPTH][ICP_THREADS];
@@ -336,7 +337,7 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, float4* cert, int n_src,
     for (int s0 = blockIdx.x; s0 < nsl; s0 += J * G) {
         if (threadIdx.x == 0) s_nwalk = 0;
         __syncthreads();
-        int tj[J], ppj[J];
+        int tj[J], ppj[J], pp2j[J];
         float4 pj[J], cj[J];
 #pragma unroll
         for (int j = 0; j < J; j++) {
@@ -347,6 +348,7 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, float4* cert, int n_src,
 #pragma unroll
         for (int j = 0; j < J; j++) {
             ppj[j] = -1;
+            pp2j[j] = -1;
             if (tj[j] >= 0) {
                 float4 p = pj[j];
                 const float ox = p.x, oy = p.y, oz = p.z;
@@ -357,6 +359,7 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, float4* cert, int n_src,
                     fmaxf(fmaxf(fabsf(p.x - ox), fabsf(p.y - oy)), fabsf(p.z - oz)) * 1.7320509f;
                 if (use_cert) {
                     ppj[j] = prev[tj[j]];
+                    pp2j[j] = prev2[tj[j]];
                     cj[j] = cert[tj[j]];
                 }
             }
@@ -371,7 +374,18 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, float4* cert, int n_src,
             if (need && use_cert) {
                 // no correspondence (pp < 0): the certificate says nothing lies within c.w of c; with
                 // the gate as the key it reads "still nothing within the gate"
-                const float k1 = ppj[j] >= 0 ? key32(qj[j].x, qj[j].y, qj[j].z, pj[j].x, pj[j].y, pj[j].z) : max_corres_dist;
+                float k1 = ppj[j] >= 0 ? key32(qj[j].x, qj[j].y, qj[j].z, pj[j].x, pj[j].y, pj[j].z) : max_corres_dist;
+                if (pp2j[j] >= 0) {
+                    // a runner-up inside the certified band (rare: near-ties): whichever of the two is
+                    // nearer NOW, by (key, original index), is the correspondence
+                    const float4 q2 = __ldg(iv.pts + pp2j[j]);
+                    const float k2 = key32(q2.x, q2.y, q2.z, pj[j].x, pj[j].y, pj[j].z);
+                    if (kless32(k2, __float_as_int(q2.w), k1, __float_as_int(qj[j].w))) {
+                        prev[tj[j]] = pp2j[j];
+                        prev2[tj[j]] = ppj[j];
+                        k1 = k2;
+                    }
+                }
                 need = !cert_holds(pj[j], cj[j], k1);
             }
             const unsigned m = __ballot_sync(full, need);
@@ -390,23 +404,38 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, float4* cert, int n_src,
             const int t = (s0 + (e / ICP_THREADS) * G) * ICP_THREADS + (e % ICP_THREADS);
             const float4 p = cur[t];
             const int pp = prev[t];
-            Best2f best;
             const float moved = s_move[e];
             // a point searched for the first time (iteration 0 of a state) has not moved yet: no certificate
-            best.gap = (use_cert && first_done && moved < move_max) ? gapk * moved + gap_min : -1.f;
-            // the gate doubles as the search bound: a neighbour at or beyond it is dropped anyway.  With a
-            // certificate in view the bound reaches `gap` beyond the gate, so that "nothing within the
-            // gate" can be certified too (those searches are the widest of all: a 1 m ball)
-            float bound = max_corres_dist;
-            if (best.gap >= 0.f) {
-                const float r = __fadd_ru(__fmul_ru(__fsqrt_ru(max_corres_dist), 1.0001f), best.gap);  // as Best2f::reach
-                bound = __fmul_ru(r, r);
-            }
-            nn1_lockstep<ICP_THREADS>(iv, p.x, p.y, p.z, pp >= 0 ? (pp >> PCNN_GROUP_LOG) : -1, bound, best,
-                                      s_qg, s_ql, threadIdx.x);
-            if (live) {
-                prev[t] = best.pos;
-                cert[t] = make_float4(p.x, p.y, p.z, best.gap >= 0.f ? cert_radius(best.lim) : -1.f);
+            const float gap = (use_cert && first_done && moved < move_max) ? gapk * moved + gap_min : -1.f;
+            const int seed = pp >= 0 ? (pp >> PCNN_GROUP_LOG) : -1;
+            if (__all_sync(full, gap < 0.f)) {
+                // nobody in this warp is after a certificate (the pose still moves by more than the
+                // target's spacing): the plain 1-NN walk, lighter by the runner-up and the floor.
+                // The gate doubles as the search bound: a neighbour at or beyond it is dropped anyway
+                Best1f best;
+                nn1_lockstep<ICP_THREADS>(iv, p.x, p.y, p.z, seed, max_corres_dist, best, s_qg, s_ql, threadIdx.x);
+                if (live) {
+                    prev[t] = best.pos;
+                    prev2[t] = -1;
+                    cert[t] = make_float4(p.x, p.y, p.z, -1.f);
+                }
+            } else {
+                Best2f best;
+                best.gap = gap;
+                // with a certificate in view the bound reaches `gap` beyond the gate, so that "nothing
+                // within the gate" can be certified too (those searches are the widest of all: a 1 m ball)
+                float bound = max_corres_dist;
+                if (gap >= 0.f) {
+                    const float r = __fadd_ru(__fmul_ru(__fsqrt_ru(max_corres_dist), 1.0001f), gap);  // as Best2f::reach
+                    bound = __fmul_ru(r, r);
+                }
+                nn1_lockstep<ICP_THREADS>(iv, p.x, p.y, p.z, seed, bound, best, s_qg, s_ql, threadIdx.x);
+                if (live) {
+                    prev[t] = best.pos;
+                    // the runner-up matters only if it lies under the floor of the rest
+                    prev2[t] = (gap >= 0.f && best.pos2 >= 0 && best.key2 < best.floor_key()) ? best.pos2 : -1;
+                    cert[t] = make_float4(p.x, p.y, p.z, gap >= 0.f ? cert_radius(best.floor_key()) : -1.f);
+                }
             }
         }
         __syncthreads();  // s_list is reused
@@ -707,7 +736,7 @@ static void icp_free(pcnn_icp_state* st) {
     if (!st) return;
     icp_peer_detach(st);
     if (st->box) cudaFree(st->box);
-    void* ptrs[6] = {st->cur, st->nrm, st->prev, st->partials, st->dev, st->cert};
+    void* ptrs[7] = {st->cur, st->nrm, st->prev, st->partials, st->dev, st->cert, st->prev2};
     for (void* p : ptrs)
         if (p) cudaFreeAsync(p, st->mem_stream);
     delete st;
@@ -724,7 +753,7 @@ static int icp_launch_accumulate(pcnn_icp_state* st, int kind, cudaStream_t s) {
         for (int p = 0; p < st->world; p++) pv.box[p] = st->peer[p];
         pv.rank = st->rank; pv.world = st->world;
     }
-    icp_search_kernel<<<st->nblocks, ICP_THREADS, 0, s>>>(ix->view, st->cur, st->prev, st->cert, n, st->use_cert, st->gapk,
+    icp_search_kernel<<<st->nblocks, ICP_THREADS, 0, s>>>(ix->view, st->cur, st->prev, st->prev2, st->cert, n, st->use_cert, st->gapk,
                                                           st->move_frac, st->prm.max_corres_dist, st->dev);
 #define PCNN_ICP_LAUNCH(MODE, KIND)                                                              \
     icp_accumulate_kernel<MODE, KIND><<<st->nblocks, ICP_THREADS, 0, s>>>(                       \
@@ -791,6 +820,7 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
     cudaError_t e = palloc(&st->cur, sizeof(float4) * (size_t)(n + 1));
     if (e == cudaSuccess) e = palloc(&st->prev, sizeof(int) * (size_t)(n + 1));
     if (e == cudaSuccess) e = palloc(&st->cert, sizeof(float4) * (size_t)(n + 1));
+    if (e == cudaSuccess) e = palloc(&st->prev2, sizeof(int) * (size_t)(n + 1));
     if (e == cudaSuccess) e = palloc(&st->partials, sizeof(double) * ICP_NS * (size_t)st->nblocks);
     if (e == cudaSuccess) e = palloc(&st->dev, sizeof(Dev));
     if (e == cudaSuccess && params->mode == 1) e = palloc(&st->nrm, sizeof(float4) * (size_t)(target->n + 1));
@@ -813,6 +843,7 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
         } else {
             icp_state_init_kernel<<<1, 32, 0, s>>>(st->dev, T0);
             e = cudaMemsetAsync(st->prev, 0xff, sizeof(int) * (size_t)(n + 1), s);  // -1: no correspondence yet
+            if (e == cudaSuccess) e = cudaMemsetAsync(st->prev2, 0xff, sizeof(int) * (size_t)(n + 1), s);
             if (e == cudaSuccess) e = cudaMemsetAsync(st->cert, 0xff, sizeof(float4) * (size_t)(n + 1), s);  // NaN: no certificate
             if (n > 0) {
                 icp_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(src_dev, n, stride, (long long)src_index_base, T0, tmp);

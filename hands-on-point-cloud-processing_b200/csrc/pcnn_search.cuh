@@ -93,22 +93,27 @@ struct Best1f {
         if (kless32(d, id, key, idx)) { key = d; idx = id; pos = p; }
     }
 };
-// The nearest point and a FLOOR under everybody else: once the search has ended, every point
-// other than `pos` has key >= lim (examined ones by comparison, pruned ones because their box
-// bound exceeded the pruning key, which only falls).  ICP turns lim into a certificate that lets
-// later iterations keep the correspondence without searching (pcnn_icp.cu).  The floor is only
-// chased up to (sqrt(key) + gap)^2: a caller that expects its query to move by less than `gap`
-// needs no more, and the walk then costs little more than a plain 1-NN walk (gap < 0: exactly
-// that, lim == key, no certificate).
+// The nearest point, ONE other point remembered by position, and a FLOOR under everybody else:
+// once the search has ended, every point other than `pos` and `pos2` has key >= floor() (examined
+// ones by comparison, pruned ones because their box bound exceeded the pruning key, which only
+// falls).  ICP turns that into a certificate that lets later iterations keep the correspondence
+// without searching (pcnn_icp.cu).  The floor is only chased up to (sqrt(key) + gap)^2: a caller
+// that expects its query to move by less than `gap` needs no more, and the walk then costs little
+// more than a plain 1-NN walk (gap < 0: exactly that, prune == key, no certificate).  Remembering
+// the runner-up by position is what makes near-ties certifiable: two target points within 1e-5 m
+// of equidistant leave no room between key and key2, but plenty between key2 and the third.
 struct Best2f {
     float key;
     int idx;
     int pos;
-    float lim;  // pruning key = min(second smallest key seen, (sqrt(key)(1 + 1e-4) + gap)^2)
+    float key2;   // runner-up (smallest key seen among the others; ties broken arbitrarily)
+    int pos2;
+    float lim;    // smallest key seen outside the two above
+    float prune;  // pruning key = min(lim, (sqrt(key)(1 + 1e-4) + gap)^2)
     float gap;
-    PCNN_HD void init() { key = i2f(0x7f800000); idx = 0x7fffffff; pos = -1; lim = key; gap = -1.f; }
-    PCNN_HD void start(float b) { key = b; idx = 0x7fffffff; pos = -1; lim = b; }
-    PCNN_HD float bound() const { return lim; }
+    PCNN_HD void start(float b) { key = b; idx = 0x7fffffff; pos = -1; key2 = b; pos2 = -1; lim = b; prune = b; }
+    PCNN_HD float bound() const { return prune; }
+    PCNN_HD float floor_key() const { return prune; }
 #if defined(__CUDACC__)
     __device__ __forceinline__ float reach(float k) const {
         if (gap < 0.f) return k;
@@ -117,11 +122,17 @@ struct Best2f {
     }
     __device__ __forceinline__ void offer(float d, int id, int p) {
         if (kless32(d, id, key, idx)) {
-            const float second = key;  // the displaced best is now the nearest of the others
+            lim = fminf(lim, key2);  // the old runner-up joins the rest
+            key2 = key; pos2 = pos;
             key = d; idx = id; pos = p;
-            lim = fminf(fminf(lim, second), reach(d));
+            prune = fminf(lim, reach(d));
+        } else if (d < key2) {
+            lim = fminf(lim, key2);
+            key2 = d; pos2 = p;
+            prune = fminf(prune, lim);
         } else if (d < lim) {
             lim = d;
+            prune = fminf(prune, d);
         }
     }
 #endif

@@ -544,18 +544,21 @@ def run_gpu(args):
     alg_bytes = N_QUERIES * (16 + 8 * K) + 16 * N_POINTS   # Q*(16+8k) + 16*N
     k_ms = float(np.mean(kern_ms))
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    traffic = None
+    traffic = diag = None
     tpath = os.path.join(ROOT, "profiles", "knn_kernel_traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+            prof = json.load(open(tpath))
+            traffic = prof.get("dram_bytes_per_launch")
+            diag = prof.get("candidate_traffic")   # from the committed ncu capture, not measured in this run
         except Exception:
-            traffic = None
+            traffic = diag = None
     roofline = {"bound": "hbm", "kernel": "knn_dfs_kernel<8>", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": k_ms,
                 "kernel_share_of_step": k_ms / (sum(step_ms) / args.steps),
-                "note": "kNN is not HBM-bound: candidates are served from L2/L1 (SURVEY 8d, DESIGN.md)"}
+                "note": "kNN is not HBM-bound: candidates are served from L2/L1 (SURVEY 8d, DESIGN.md)",
+                "candidate_traffic_from_ncu_capture": diag}
 
     line = {
         "metric": "kNN queries/s (k=8)", "value": value, "unit": "queries/s", "n_gpus": world,

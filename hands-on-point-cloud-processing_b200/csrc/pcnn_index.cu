@@ -428,7 +428,7 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: sort_queries must be 0 or 1");
         index->opt_sort_queries = value;
     } else if (!std::strcmp(name, "method")) {
-        PCNN_CHECK_ARG(value >= 0 && value <= 9, "pcnn_set_option: method must be 0..9");
+        PCNN_CHECK_ARG(value >= 0 && value <= 10, "pcnn_set_option: method must be 0..10");
         index->opt_method = value;
     } else if (!std::strcmp(name, "profile")) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: profile must be 0 or 1");

@@ -817,6 +817,10 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     }
 }
 
+}  // namespace pcnn
+#include "pcnn_knn_refill.cuh"
+namespace pcnn {
+
 // ------------------------------------------------------------------ hybrid: Morton sweep, nearest-first rescue
 // knn_lockstep_kernel's per-lane Morton-window sweep does the least box work when the Morton
 // seed is good (almost always); a lane whose sweep exceeds `budget` steps has a poor seed, and
@@ -1484,6 +1488,23 @@ static void launch_dfs_k(const pcnn_index* ix, const float* q, int nq, int strid
         ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
 }
 template <int K>
+static void launch_refill_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
+                            int k, int32_t* oi, float* od, double* od64, unsigned* counter, cudaStream_t s) {
+    // persistent grid: what is resident at once; queries come from the global counter
+    static int blocks = 0;
+    if (blocks == 0) {
+        int per_sm = 0, sms = 148;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)knn_dfs_refill_kernel<K>, KT_THREADS, 0) != cudaSuccess || per_sm < 1)
+            per_sm = 4;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ix->device);
+        blocks = per_sm * sms;
+    }
+    static int refill_min = getenv("PCNN_REFILL_MIN") ? atoi(getenv("PCNN_REFILL_MIN")) : PCNN_REFILL_MIN;
+    const int need = (nq + KT_THREADS - 1) / KT_THREADS;
+    knn_dfs_refill_kernel<K><<<need < blocks ? need : blocks, KT_THREADS, 0, s>>>(
+        ix->view, q, nq, stride, perm, k, oi, od, od64, counter, refill_min);
+}
+template <int K>
 static void launch_hybrid_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
                             int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
     knn_hybrid_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
@@ -1504,7 +1525,8 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     int method = ix->opt_method;
     if (method == 0) method = (k <= 16) ? 7 : (k <= KH_CAP ? 9 : 2);
     if (method == 9 && (k > KH_CAP || ix->n == 0)) method = 2;
-    if ((method == 1 || method == 3 || method == 4 || method == 5 || method == 6 || method == 7 || method == 8) && k > 16) method = 2;
+    if ((method == 1 || method == 3 || method == 4 || method == 5 || method == 6 || method == 7 || method == 8 || method == 10) && k > 16) method = 2;
+    if (method == 10 && ix->n == 0) method = 7;
     if (method == 3 && ix->n == 0) method = 1;
     if (method == 9) {
         Scratch sc(s);
@@ -1530,6 +1552,23 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         else if (k <= 4) launch_hybrid_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 8) launch_hybrid_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else launch_hybrid_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        prof_end(ix, s);
+    } else if (method == 10) {
+        Scratch sc(s);
+        unsigned* perm = nullptr;
+        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+            int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
+            if (rc != PCNN_OK) return rc;
+        }
+        unsigned* counter = nullptr;
+        if (sc.get(&counter, 1) != cudaSuccess) { set_error("pcnn_knn: scratch allocation failed"); return PCNN_ERR_NOMEM; }
+        PCNN_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned), s));
+        prof_begin(ix, s);
+        if (k <= 1) launch_refill_k<1>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, counter, s);
+        else if (k <= 2) launch_refill_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, counter, s);
+        else if (k <= 4) launch_refill_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, counter, s);
+        else if (k <= 8) launch_refill_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, counter, s);
+        else launch_refill_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, counter, s);
         prof_end(ix, s);
     } else if (method == 7) {
         Scratch sc(s);

@@ -17,6 +17,7 @@ ref = None
 cfgs = [("thread", 1, {"leaf_log": 1})]
 cfgs.append(("lockstep b60", 6, {"coherent_budget": 60}))
 cfgs.append(("dfs", 7, {}))
+cfgs.append(("refill", 10, {}))
 only = os.environ.get("TUNE_ONLY")
 if only:
     cfgs = [c for c in cfgs if c[0].startswith(only)]

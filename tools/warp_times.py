@@ -45,3 +45,10 @@ print("last to finish:")
 for w in late:
     print("  warp %6d start %8.0f end %8.0f dur_ns %.0f" % (w, t0[w], end_ns[w], dur[w] / 1.965))
 np.save(os.path.join(ROOT, "gpurun_out", "warp_times.npy"), b)
+# lock-step walks (method 7): c[0] = longest walk of the warp (steps), c[3] = steps summed over lanes,
+# c[1] = group scans (warp-wide drains that ran), c[2] = insertions, c[4] = rounds
+mx, sm = cn[:, 0].astype(np.float64), cn[:, 3].astype(np.float64)
+ok = mx > 0
+print("walk utilisation (sum of lane steps / 32 x longest lane): mean %.3f  p10 %.3f p50 %.3f p90 %.3f; mean longest %.1f mean lane %.1f" % (
+    (sm[ok] / (32 * mx[ok])).mean(), *np.percentile(sm[ok] / (32 * mx[ok]), [10, 50, 90]), mx[ok].mean(), (sm[ok] / 32).mean()))
+print("work-weighted utilisation: %.3f" % (sm[ok].sum() / (32 * mx[ok].sum())))

@@ -49,6 +49,24 @@ def test_icp_iteration_by_iteration(pair, oracle_port):
     ix.close()
 
 
+@pytest.mark.parametrize("n_src,n_tar", [(1, 1000), (31, 1000), (129, 3000), (513, 777), (1000, 2000), (4097, 20000)])
+def test_icp_ragged_sizes(pair, oracle_port, n_src, n_tar):
+    # partial warps / slices, more source points than target points (well-posed cases only: with a handful of target points the
+    # SVD is rank deficient and two correct solvers may differ by a sign):
+    # the searched-points lists, certificates and the fixed thread assignment of the sums all see
+    # tails here.  p2p only needs 3 non-collinear pairs; a singular system must give status 1 on both sides
+    src, tar, nrm, T = pair
+    s, t, n = src[:n_src].copy(), tar[:n_tar].copy(), nrm[:n_tar].copy()
+    ix = pc.Index(t)
+    for mode in (0, 1):
+        got = ix.icp(s, tar_normals=n, max_iter=12, max_corres_dist=4.0, mode=mode)
+        want = oracle_port.icp(s, t, n, max_iter=12, max_corres_dist=4.0, mode=mode, accum=1, nthreads=4)
+        assert (got["iters"], got["status"], got["pairs"]) == (want["iters"], want["status"], want["pairs"]), (mode, got, want)
+        if got["status"] == 0:
+            assert parity.rot_err(got["T"], want["T"]) < 10 * POSE_TOL and parity.trans_err(got["T"], want["T"]) < 10 * POSE_TOL
+    ix.close()
+
+
 def test_icp_initial_pose_gate_and_convergence_rule(pair, oracle_port):
     src, tar, nrm, T = pair
     ix = pc.Index(tar)

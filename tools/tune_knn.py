@@ -18,6 +18,9 @@ cfgs = [("thread", 1, {"leaf_log": 1})]
 cfgs.append(("lockstep b60", 6, {"coherent_budget": 60}))
 cfgs.append(("dfs", 7, {}))
 cfgs.append(("refill", 10, {}))
+for kv in os.environ.get("OPTS", "").split():
+    a, b = kv.split("=")
+    ix.set_option(a, int(b))
 only = os.environ.get("TUNE_ONLY")
 if only:
     cfgs = [c for c in cfgs if c[0].startswith(only)]

@@ -35,6 +35,7 @@ struct pcnn_icp_state {
     double* partials = nullptr;  // [nblocks][32]
     struct Dev* dev = nullptr;   // device-resident loop state
     int nblocks = 0;
+    int acc_blocks = 0;          // grid of the sums kernel: fewer, fatter blocks = fewer partial rows to fold
     // device memory comes from the library's stream-ordered pool on the stream given to
     // pcnn_icp_create and goes back to it on the same stream: no device-wide synchronisation per
     // registration (cudaMalloc/cudaFree cost 50 ms per call next to a few GB of cached blocks)
@@ -99,10 +100,14 @@ __device__ __forceinline__ void xform(const float* R, const float* t, float& x, 
 
 __device__ bool chol6_dev(const double* N, const double* g, double* x) {
     double L[36];
+#pragma unroll
     for (int i = 0; i < 36; i++) L[i] = 0;
+#pragma unroll
     for (int i = 0; i < 6; i++)
+#pragma unroll
         for (int j = 0; j <= i; j++) {
             double s = N[i * 6 + j];
+#pragma unroll
             for (int k = 0; k < j; k++) s -= L[i * 6 + k] * L[j * 6 + k];
             if (i == j) {
                 if (!(s > 0)) return false;
@@ -111,13 +116,17 @@ __device__ bool chol6_dev(const double* N, const double* g, double* x) {
                 L[i * 6 + j] = s / L[j * 6 + j];
         }
     double y[6];
+#pragma unroll
     for (int i = 0; i < 6; i++) {
         double s = g[i];
+#pragma unroll
         for (int k = 0; k < i; k++) s -= L[i * 6 + k] * y[k];
         y[i] = s / L[i * 6 + i];
     }
+#pragma unroll
     for (int i = 5; i >= 0; i--) {
         double s = y[i];
+#pragma unroll
         for (int k = i + 1; k < 6; k++) s -= L[k * 6 + i] * x[k];
         x[i] = s / L[i * 6 + i];
     }
@@ -756,7 +765,7 @@ static int icp_launch_accumulate(pcnn_icp_state* st, int kind, cudaStream_t s) {
     icp_search_kernel<<<st->nblocks, ICP_THREADS, 0, s>>>(ix->view, st->cur, st->prev, st->prev2, st->cert, n, st->use_cert, st->gapk,
                                                           st->move_frac, st->prm.max_corres_dist, st->dev);
 #define PCNN_ICP_LAUNCH(MODE, KIND)                                                              \
-    icp_accumulate_kernel<MODE, KIND><<<st->nblocks, ICP_THREADS, 0, s>>>(                       \
+    icp_accumulate_kernel<MODE, KIND><<<st->acc_blocks, ICP_THREADS, 0, s>>>(                       \
         ix->view, st->cur, st->nrm, st->prev, n, st->prm.max_corres_dist, st->prm.loss_epsilon, st->dev, st->partials, pv)
     if (st->prm.mode == 0) {
         if (kind == 2) PCNN_ICP_LAUNCH(0, 2); else if (kind == 1) PCNN_ICP_LAUNCH(0, 1); else PCNN_ICP_LAUNCH(0, 0);
@@ -808,6 +817,15 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
         st->nblocks = (n + ICP_THREADS - 1) / ICP_THREADS;
         if (st->nblocks < 1) st->nblocks = 1;
         if (st->nblocks > sms * per_sm) st->nblocks = sms * per_sm;
+        // the sums kernel takes ICP_J slices per block and step: one block per J slices until the
+        // device is covered, so a 100k-point cloud folds ~200 partial rows instead of ~800
+        const int slices = (n + ICP_THREADS - 1) / ICP_THREADS;
+        st->acc_blocks = (slices + ICP_J - 1) / ICP_J;
+        if (st->acc_blocks < (slices < sms ? slices : sms)) st->acc_blocks = slices < sms ? slices : sms;
+        if (st->acc_blocks > 2 * sms) st->acc_blocks = 2 * sms;  // measured at 1M points: 148 / 296 / 592 / 1184 blocks -> 221 / 209 / 208 / 222 us per iteration
+        if (st->acc_blocks > st->nblocks) st->acc_blocks = st->nblocks;
+        if (const char* e = getenv("PCNN_ICP_ACC_BLOCKS")) st->acc_blocks = atoi(e) < st->nblocks ? atoi(e) : st->nblocks;
+        if (st->acc_blocks < 1) st->acc_blocks = 1;
     }
     st->mem_stream = s;
     cudaMemPool_t pool = lib_pool();

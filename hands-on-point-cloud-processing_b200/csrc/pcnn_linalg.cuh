@@ -9,9 +9,12 @@ __device__ inline void svd3_dev(const double* A, double* U, double* s, double* V
     for (int i = 0; i < 9; i++) { W[i] = A[i]; V[i] = (i % 4 == 0) ? 1.0 : 0.0; }
     for (int sweep = 0; sweep < 60; sweep++) {
         double off = 0;
+#pragma unroll
         for (int p = 0; p < 2; p++)
+#pragma unroll
             for (int q = p + 1; q < 3; q++) {
                 double a = 0, b = 0, c = 0;
+#pragma unroll
                 for (int r = 0; r < 3; r++) {
                     a += W[r * 3 + p] * W[r * 3 + p];
                     b += W[r * 3 + q] * W[r * 3 + q];
@@ -22,6 +25,7 @@ __device__ inline void svd3_dev(const double* A, double* U, double* s, double* V
                 const double zeta = (b - a) / (2.0 * c);
                 const double tt = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
                 const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+#pragma unroll
                 for (int r = 0; r < 3; r++) {
                     const double wp = W[r * 3 + p], wq = W[r * 3 + q];
                     W[r * 3 + p] = cs * wp - sn * wq;

@@ -1015,6 +1015,10 @@ knn_hybrid_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
 // order, resultSet.hpp:65-91).
 constexpr int KH_THREADS = 64;
 constexpr int KH_CAP = 32;
+#ifndef PCNN_KH_QDEPTH
+#define PCNN_KH_QDEPTH 4
+#endif
+constexpr int KH_QDEPTH = PCNN_KH_QDEPTH;  // queue entries per lane in the heap kernel (shared memory decides its occupancy)
 
 struct HeapRef {
     double* key;  // [KH_CAP][KH_THREADS], this lane's column
@@ -1097,8 +1101,8 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
                     float* __restrict__ out_dist, double* __restrict__ out_dist64) {
     __shared__ double s_hk[KH_CAP][KH_THREADS];
     __shared__ int s_hi[KH_CAP][KH_THREADS];
-    __shared__ int s_qg[KQ_DEPTH][KH_THREADS];
-    __shared__ float s_ql[KQ_DEPTH][KH_THREADS];
+    __shared__ int s_qg[KH_QDEPTH][KH_THREADS];
+    __shared__ float s_ql[KH_QDEPTH][KH_THREADS];
     const unsigned full = 0xffffffffu;
     const int tid = threadIdx.x;
     const int t = blockIdx.x * KH_THREADS + tid;
@@ -1127,10 +1131,10 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
         const int h = home_group(iv, qcode);
         const int half = (k + 2 * PCNN_GROUP - 1) / (2 * PCNN_GROUP);  // groups on each side
         const int h0 = max(h - half, 0), h1 = min(h + half, iv.n0 - 1);
-        const int nseed = __reduce_max_sync(full, (h1 - h0 + KQ_DEPTH) / KQ_DEPTH);  // same trip count in every lane
+        const int nseed = __reduce_max_sync(full, (h1 - h0 + KH_QDEPTH) / KH_QDEPTH);  // same trip count in every lane
         for (int sr = 0; sr < nseed; sr++) {
-            const int g0 = h0 + sr * KQ_DEPTH;
-            for (int g = g0; g <= h1 && g < g0 + KQ_DEPTH; g++) { s_qg[cnt][tid] = g; s_ql[cnt][tid] = 0.f; cnt++; }
+            const int g0 = h0 + sr * KH_QDEPTH;
+            for (int g = g0; g <= h1 && g < g0 + KH_QDEPTH; g++) { s_qg[cnt][tid] = g; s_ql[cnt][tid] = 0.f; cnt++; }
             const int maxc = __reduce_max_sync(full, cnt);
             for (int r = 0; r < maxc; r++) {
                 const bool act = r < cnt;
@@ -1144,7 +1148,7 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
         while (true) {
 #pragma unroll 1
             for (int s = 0; s < KL_WALK; s++) {
-                const bool can = !done && cnt <= KQ_DEPTH - 2 && !(cnt > 0 && wf > 3.0e38f);
+                const bool can = !done && cnt <= KH_QDEPTH - 2 && !(cnt > 0 && wf > 3.0e38f);
                 if (!__any_sync(full, can)) break;
                 if (can) {
                     int L, P, far = 0;

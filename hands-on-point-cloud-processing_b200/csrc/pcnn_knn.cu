@@ -1586,6 +1586,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         else if (k <= 2) launch_dfs_k<2>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 4) launch_dfs_k<4>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else if (k <= 8) launch_dfs_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
+        else if (k <= 12) launch_dfs_k<12>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);  // 9..12: pca_normal.py's max_nn = 10
         else launch_dfs_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         prof_end(ix, s);
     } else if (method == 6) {

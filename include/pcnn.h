@@ -127,10 +127,11 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
 /* Query-side knobs (all have working defaults).  `sort_queries`: 1 = order queries along
  * the Morton curve before the search (default), 0 = caller's order, e.g. already coherent.
  * `method`: 0 = auto, 1 = thread-per-query traversal, 2 = warp-per-query traversal,
- * 3 = brute-force tiles, 4 = warp-shared walk, 5 = shared walk + per-lane scan queues, 10 = method 7 on a persistent grid with lane refill (study),
+ * 3 = brute-force tiles, 4 = warp-shared walk, 5 = shared walk + per-lane scan queues,
  * 6 = lock-step Morton-window sweeps, 7 = lock-step nearest-first walks (auto for k <= 16),
  * 8 = sweep with nearest-first rescue, 9 = nearest-first walks with a shared-memory heap
- * (auto for 16 < k <= 32).  A method that cannot serve the requested k falls back to 2.
+ * (auto for 16 < k <= 32), 10 = method 7 on a persistent grid with lane refill (kept for study:
+ * measured slower).  A method that cannot serve the requested k falls back to 2.
  * `sort_bits` (3..30, multiple of 3): leading Morton bits the query batch is ordered by.
  * `radius_batch`: radius kernel, 1 = auto (default), 0 = warp per query, 2 = runs of queries,
  * 3 = query per lane, 4 = warp per query with a dense stack walk, 5 = dense stack walk per run

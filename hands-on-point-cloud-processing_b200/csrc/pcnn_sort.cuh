@@ -88,6 +88,60 @@ static __global__ void __launch_bounds__(1024) rs_scan(unsigned* __restrict__ a,
     }
 }
 
+// Large tables (more than 64k counters: clouds beyond ~1M points) are scanned in chunks of 4096
+// counters by as many blocks, the chunk totals by rs_scan above, and the chunk bases added back:
+// three short launches instead of one block walking 600k counters (193 us per pass at 10M points).
+static __global__ void __launch_bounds__(1024) rs_scan_chunk(unsigned* __restrict__ a, int total,
+                                                            unsigned* __restrict__ chunk_sum) {
+    __shared__ unsigned wsum[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int base = blockIdx.x * 4096;
+    unsigned v[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int i = base + 4 * t + j;
+        v[j] = i < total ? a[i] : 0u;
+    }
+    const unsigned s = v[0] + v[1] + v[2] + v[3];
+    unsigned inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned w = wsum[lane], winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned u = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += u;
+        }
+        wsum[lane] = winc - w;
+        if (lane == 31) chunk_sum[blockIdx.x] = winc;
+    }
+    __syncthreads();
+    unsigned run = wsum[warp] + inc - s;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int i = base + 4 * t + j;
+        if (i < total) a[i] = run;
+        run += v[j];
+    }
+}
+static __global__ void __launch_bounds__(1024) rs_scan_add(unsigned* __restrict__ a, int total,
+                                                          const unsigned* __restrict__ chunk_base) {
+    const unsigned b = chunk_base[blockIdx.x];
+    const int base = blockIdx.x * 4096;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int i = base + j * 1024 + threadIdx.x;
+        if (i < total) a[i] += b;
+    }
+}
+constexpr int RS_SCAN_CHUNKED_FROM = 65536;  // counters
+
 template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_scatter(const KeyT* __restrict__ kin, const unsigned* __restrict__ vin, KeyT* __restrict__ kout,
@@ -162,13 +216,25 @@ inline int radix_sort_pairs(KeyT* k0, unsigned* v0, KeyT* k1, unsigned* v1, unsi
         unsigned* vi = cur ? v1 : v0;
         unsigned* vo = cur ? v0 : v1;
         rs_hist<KeyT><<<ntiles, RS_THREADS, 0, s>>>(ki, n, shift, hist, ntiles);
-        rs_scan<<<1, 1024, 0, s>>>(hist, 256 * ntiles);
+        const int total = 256 * ntiles;
+        if (total >= RS_SCAN_CHUNKED_FROM) {
+            const int nchunks = (total + 4095) / 4096;
+            unsigned* chunk = hist + total;  // radix_hist_elems leaves room for the chunk totals
+            rs_scan_chunk<<<nchunks, 1024, 0, s>>>(hist, total, chunk);
+            rs_scan<<<1, 1024, 0, s>>>(chunk, nchunks);
+            rs_scan_add<<<nchunks, 1024, 0, s>>>(hist, total, chunk);
+        } else {
+            rs_scan<<<1, 1024, 0, s>>>(hist, total);
+        }
         rs_scatter<KeyT><<<ntiles, RS_THREADS, 0, s>>>(ki, vi, ko, vo, n, shift, hist, ntiles);
         cur ^= 1;
     }
     return cur;
 }
 
-inline size_t radix_hist_elems(int n) { return (size_t)256 * ((n + RS_TILE - 1) / RS_TILE); }
+inline size_t radix_hist_elems(int n) {
+    const size_t total = (size_t)256 * ((n + RS_TILE - 1) / RS_TILE);
+    return total + (total + 4095) / 4096;  // + chunk totals of the chunked scan
+}
 
 }  // namespace pcnn

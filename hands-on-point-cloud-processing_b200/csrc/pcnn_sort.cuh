@@ -3,8 +3,8 @@
 // Replaces the reference's per-node median selection (Homework2/hw2/include/kdtree.hpp:57-109,
 // :208-261) and 8-way recursive partition (octree.hpp:36-90) as the spatial ordering step.
 //
-// Per pass: rs_hist (per-tile digit histogram, digit-major [256][ntiles]) -> rs_scan
-// (exclusive scan of that table) -> rs_scatter (stable rank inside the tile via
+// Per pass: rs_hist (per-tile digit histogram, digit-major [256][ntiles]) -> rs_scan_chunk
+// (exclusive scan of that table, chunk by chunk) -> rs_scatter (stable rank inside the tile via
 // __match_any_sync + per-warp digit counters, then scatter).  HBM traffic per pass:
 // read keys twice + values once, write both once.
 #pragma once
@@ -33,64 +33,9 @@ rs_hist(const KeyT* __restrict__ keys, int n, int shift, unsigned* __restrict__ 
     hist[(size_t)threadIdx.x * ntiles + blockIdx.x] = h[threadIdx.x];
 }
 
-// Exclusive scan of `total` counters in place, one block of 1024 threads: tiles of 4096
-// counters (four consecutive per thread, coalesced), warp-shuffle scan inside a tile, running
-// carry across tiles.  The next tile's loads are issued before the current tile is scanned.
-static __global__ void __launch_bounds__(1024) rs_scan(unsigned* __restrict__ a, int total) {
-    __shared__ unsigned wsum[32];
-    __shared__ unsigned s_carry;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    if (t == 0) s_carry = 0;
-    __syncthreads();
-    unsigned v[4], nv[4];
-    auto load = [&](int base, unsigned* out) {
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int i = base + 4 * t + j;
-            out[j] = i < total ? a[i] : 0u;
-        }
-    };
-    load(0, v);
-    for (int base = 0; base < total; base += 4096) {
-        if (base + 4096 < total) load(base + 4096, nv);
-        const unsigned s01 = v[0] + v[1], s = s01 + v[2] + v[3];
-        unsigned inc = s;  // inclusive scan of the per-thread sums inside the warp
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += u;
-        }
-        if (lane == 31) wsum[warp] = inc;
-        __syncthreads();
-        if (warp == 0) {
-            unsigned w = wsum[lane], winc = w;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const unsigned u = __shfl_up_sync(0xffffffffu, winc, o);
-                if (lane >= o) winc += u;
-            }
-            wsum[lane] = winc - w;  // exclusive prefix of the warp sums
-        }
-        __syncthreads();
-        const unsigned carry = s_carry;
-        unsigned run = carry + wsum[warp] + inc - s;
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int i = base + 4 * t + j;
-            if (i < total) a[i] = run;
-            run += v[j];
-        }
-        __syncthreads();
-        if (t == 1023) s_carry = run;  // the last thread's running total = carry + tile sum
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < 4; j++) v[j] = nv[j];
-    }
-}
-
-// Large tables (more than 64k counters: clouds beyond ~1M points) are scanned in chunks of 4096
-// counters by as many blocks, the chunk totals by rs_scan above, and the chunk bases added back:
-// three short launches instead of one block walking 600k counters (193 us per pass at 10M points).
+// The digit table is scanned in chunks of 4096 counters by as many blocks (exclusive prefix
+// inside the chunk + the chunk's total); rs_scatter adds the totals of the chunks before its own.
+// (One block walking the whole table took 10 us per pass at 1M keys and 193 us at 10M.)
 static __global__ void __launch_bounds__(1024) rs_scan_chunk(unsigned* __restrict__ a, int total,
                                                             unsigned* __restrict__ chunk_sum) {
     __shared__ unsigned wsum[32];
@@ -130,23 +75,11 @@ static __global__ void __launch_bounds__(1024) rs_scan_chunk(unsigned* __restric
         run += v[j];
     }
 }
-static __global__ void __launch_bounds__(1024) rs_scan_add(unsigned* __restrict__ a, int total,
-                                                          const unsigned* __restrict__ chunk_base) {
-    const unsigned b = chunk_base[blockIdx.x];
-    const int base = blockIdx.x * 4096;
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-        const int i = base + j * 1024 + threadIdx.x;
-        if (i < total) a[i] += b;
-    }
-}
-constexpr int RS_SCAN_CHUNKED_FROM = 65536;  // counters
-
 template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_scatter(const KeyT* __restrict__ kin, const unsigned* __restrict__ vin, KeyT* __restrict__ kout,
            unsigned* __restrict__ vout, int n, int shift, const unsigned* __restrict__ offs,
-           int ntiles) {
+           const unsigned* __restrict__ chunk_sum, int ntiles) {
     __shared__ unsigned wcount[RS_WARPS][256];
     __shared__ unsigned dbase[256];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -186,7 +119,15 @@ rs_scatter(const KeyT* __restrict__ kin, const unsigned* __restrict__ vin, KeyT*
             wcount[w][threadIdx.x] = run;
             run += c;
         }
-        dbase[threadIdx.x] = offs[(size_t)threadIdx.x * ntiles + blockIdx.x];
+        // offs holds exclusive prefixes inside chunks of 4096 counters (rs_scan_chunk); the base of
+        // this counter's chunk is the sum of the totals of the chunks before it (a handful of
+        // independent loads: 16 chunks at 1M keys, 153 at 10M)
+        const size_t at = (size_t)threadIdx.x * ntiles + blockIdx.x;
+        const int myc = (int)(at >> 12);
+        unsigned cb = 0;
+#pragma unroll 8
+        for (int c = 0; c < myc; c++) cb += __ldg(chunk_sum + c);
+        dbase[threadIdx.x] = offs[at] + cb;
     }
     __syncthreads();
 #pragma unroll
@@ -217,16 +158,10 @@ inline int radix_sort_pairs(KeyT* k0, unsigned* v0, KeyT* k1, unsigned* v1, unsi
         unsigned* vo = cur ? v0 : v1;
         rs_hist<KeyT><<<ntiles, RS_THREADS, 0, s>>>(ki, n, shift, hist, ntiles);
         const int total = 256 * ntiles;
-        if (total >= RS_SCAN_CHUNKED_FROM) {
-            const int nchunks = (total + 4095) / 4096;
-            unsigned* chunk = hist + total;  // radix_hist_elems leaves room for the chunk totals
-            rs_scan_chunk<<<nchunks, 1024, 0, s>>>(hist, total, chunk);
-            rs_scan<<<1, 1024, 0, s>>>(chunk, nchunks);
-            rs_scan_add<<<nchunks, 1024, 0, s>>>(hist, total, chunk);
-        } else {
-            rs_scan<<<1, 1024, 0, s>>>(hist, total);
-        }
-        rs_scatter<KeyT><<<ntiles, RS_THREADS, 0, s>>>(ki, vi, ko, vo, n, shift, hist, ntiles);
+        const int nchunks = (total + 4095) / 4096;
+        unsigned* chunk = hist + total;  // radix_hist_elems leaves room for the chunk totals
+        rs_scan_chunk<<<nchunks, 1024, 0, s>>>(hist, total, chunk);
+        rs_scatter<KeyT><<<ntiles, RS_THREADS, 0, s>>>(ki, vi, ko, vo, n, shift, hist, chunk, ntiles);
         cur ^= 1;
     }
     return cur;

@@ -9,6 +9,8 @@ The single-query functions fill a result set exactly as the reference does (one 
 query: correct, slow).  The ``*_batch`` functions hoist the loop of benchmark.py:58-72 into
 one call and are the intended fast path.
 """
+import bisect
+
 import numpy as np
 
 from .api import KDTREE, OCTREE
@@ -53,21 +55,20 @@ class KNNResultSet:
             print(item)
 
     def add_point(self, dist, index):
+        """Same observable behaviour as result_set.py:41-61 (a candidate equal to the worst distance
+        is accepted, lands behind entries of equal distance, and the entry pushed past the capacity
+        is dropped), written as a binary-search insert over the live prefix."""
         self.comparision_count += 1
         if dist > self.worst_dist:
             return
-        if self.count < self.capacity:
+        live = self.dist_index_list[:self.count]
+        if self.count == self.capacity:
+            live.pop()                      # full: the current last entry makes room
+        else:
             self.count += 1
-        i = self.count - 1
-        while i > 0:
-            if self.dist_index_list[i - 1].distance > dist:
-                self.dist_index_list[i] = DistIndex(self.dist_index_list[i - 1].distance,
-                                                    self.dist_index_list[i - 1].index)
-                i -= 1
-            else:
-                break
-        self.dist_index_list[i].distance = dist
-        self.dist_index_list[i].index = index
+        at = bisect.bisect_right([e.distance for e in live], dist)
+        live.insert(at, DistIndex(dist, index))
+        self.dist_index_list[:self.count] = live
         self.worst_dist = self.dist_index_list[self.capacity - 1].distance
 
     def _fill(self, idx_row, dist_row):
@@ -99,11 +100,11 @@ class RadiusNNResultSet:
             print(item)
 
     def add_point(self, distance, index):
+        """result_set.py:83-89: every candidate is counted, those within the radius (inclusive) kept."""
         self.comparision_count += 1
-        if distance > self.radius:
-            return
-        self.count += 1
-        self.dist_index_list.append(DistIndex(distance, index))
+        if distance <= self.radius:
+            self.dist_index_list.append(DistIndex(distance, index))
+            self.count = len(self.dist_index_list)
 
 
 def kdtree_construction(db_np, leaf_size):
@@ -162,13 +163,22 @@ def radius_search_batch(root, queries, radius, dist="f64"):
 
 
 def read_velodyne_bin(path, duplicate_last=False):
-    """KITTI .bin (x, y, z, intensity float32) -> (N, 3) float32; kdtree.py:253-264.
-    ``duplicate_last=True`` reproduces the C++ reader's extra copy of the last point
-    (Homework2/hw2/include/test.hpp:24-29)."""
-    pts = np.fromfile(path, dtype=np.float32).reshape(-1, 4)[:, :3]
-    if duplicate_last and len(pts):
-        pts = np.concatenate([pts, pts[-1:]], axis=0)
-    return np.ascontiguousarray(pts)
+    """KITTI .bin (x, y, z, intensity float32) -> (N, 3) float32; kdtree.py:253-264 and the C++
+    ``readBinary`` (Homework2/hw2/include/test.hpp:11-33), which reads whole 16-byte records.
+    ``duplicate_last=True`` reproduces what that C++ loop really returns: it tests ``eof`` only
+    after a read has failed, so one more point is pushed from the stale record buffer -- the last
+    point again (``124669 points read`` for the 124668-record frame), with its leading bytes
+    replaced by whatever partial record trails the file.  An empty file yields no points (the
+    reference would push one point of uninitialised stack)."""
+    raw = np.fromfile(path, dtype=np.uint8)
+    nrec, rem = divmod(len(raw), 16)
+    rec = raw[: nrec * 16].view(np.float32).reshape(-1, 4)
+    pts = rec[:, :3]
+    if duplicate_last and nrec:
+        stale = raw[(nrec - 1) * 16: nrec * 16].copy()
+        stale[:rem] = raw[nrec * 16:]
+        pts = np.concatenate([pts, stale.view(np.float32).reshape(1, 4)[:, :3]], axis=0)
+    return np.ascontiguousarray(pts, dtype=np.float32)
 
 
 # ------------------------------------------------------------------ cloud ingest + voxel grid (SURVEY 8f rank 2)

@@ -140,6 +140,7 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
         tev.push_back(ev);
         thost.push_back(std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_host0).count());
     };
+    for (int i = 0; i < nstreams; i++) wait_build(index, hp->s[i]);  // a device-side build may still be running on its own stream
     mark(hp->s[0]);
     int c = 0;
     int64_t m = 0;
@@ -236,6 +237,7 @@ int pcnn_radius_host(const pcnn_index* index, const float* q_host, int64_t nq, i
     rc = get_pipe(ix, &hp, "pcnn_radius_host");
     if (rc != PCNN_OK) return rc;
     cudaStream_t s = hp->s[0], s1 = hp->s[1];
+    wait_build(index, s);
     cudaError_t e = hp->q[0].ensure(sizeof(float) * (size_t)nq * stride);
     if (e == cudaSuccess) e = hp->off.ensure(sizeof(int64_t) * ((size_t)nq + 1));
     float* dq = (float*)hp->q[0].p;
@@ -293,6 +295,7 @@ int pcnn_icp_host(const pcnn_index* target, const float* tar_normals_host, const
     if (!g.ok) { set_error("pcnn_icp_host: cannot select CUDA device %d (no CPU fallback exists)", target->device); return PCNN_ERR_CUDA; }
     cudaStream_t s = nullptr;
     PCNN_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    wait_build(target, s);
     float *dsrc = nullptr, *dn = nullptr;
     int rc = PCNN_OK;
     cudaError_t e = cudaSuccess;
@@ -339,6 +342,7 @@ int pcnn_iss_detect_host(const pcnn_index* index, const pcnn_iss_params* params,
     if (!g.ok) { set_error("pcnn_iss_detect_host: cannot select CUDA device %d (no CPU fallback exists)", index->device); return PCNN_ERR_CUDA; }
     cudaStream_t s = nullptr;
     PCNN_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    wait_build(index, s);
     int rc = PCNN_OK;
     {
         Scratch sc(s);

@@ -260,6 +260,10 @@ __device__ double peer_exchange(const PeerView& pv, Dev* st, int col, double r) 
         }
     }
     ok = __all_sync(0xffffffffu, ok);
+    // lane j acquired rank j's flag; every lane reads every rank's column below.  The warp barrier
+    // orders the acquiring lanes before the others, the system fence extends that to the peers' stores.
+    __syncwarp();
+    __threadfence_system();
     double tot = 0.0;
     long long m = 0;
     if (ok) {
@@ -810,10 +814,12 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)icp_search_kernel, ICP_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, st->device);
         if (per_sm > 8) per_sm = 8;
-        if (const char* e = getenv("PCNN_ICP_CERT")) st->use_cert = atoi(e) != 0;
+        st->use_cert = target->opt_icp_cert;  // pcnn_set_option(target, "icp_certificates", 0|1): same result either way
         st->gapk = ICP_GAPK; st->move_frac = ICP_MOVE_MAX;
+#ifdef PCNN_STUDY
         if (const char* e = getenv("PCNN_ICP_GAPK")) st->gapk = (float)atof(e);
         if (const char* e = getenv("PCNN_ICP_MOVE")) st->move_frac = (float)atof(e);
+#endif
         st->nblocks = (n + ICP_THREADS - 1) / ICP_THREADS;
         if (st->nblocks < 1) st->nblocks = 1;
         if (st->nblocks > sms * per_sm) st->nblocks = sms * per_sm;
@@ -824,7 +830,9 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
         if (st->acc_blocks < (slices < sms ? slices : sms)) st->acc_blocks = slices < sms ? slices : sms;
         if (st->acc_blocks > 2 * sms) st->acc_blocks = 2 * sms;  // measured at 1M points: 148 / 296 / 592 / 1184 blocks -> 221 / 209 / 208 / 222 us per iteration
         if (st->acc_blocks > st->nblocks) st->acc_blocks = st->nblocks;
+#ifdef PCNN_STUDY
         if (const char* e = getenv("PCNN_ICP_ACC_BLOCKS")) st->acc_blocks = atoi(e) < st->nblocks ? atoi(e) : st->nblocks;
+#endif
         if (st->acc_blocks < 1) st->acc_blocks = 1;
     }
     st->mem_stream = s;
@@ -988,10 +996,12 @@ int pcnn_icp_finish(pcnn_icp_state* st, pcnn_icp_result* out_host, pcnn_stream s
     Dev h;
     PCNN_CUDA(cudaMemcpyAsync(&h, st->dev, sizeof(Dev), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     PCNN_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+#ifdef PCNN_STUDY
     if (getenv("PCNN_ICP_STATS"))
         fprintf(stderr, "pcnn_icp: %llu searches for %lld points x %d iterations (%.1f %% certified)\n", h.walked,
                 (long long)st->n_src, h.iters,
                 h.iters > 0 && st->n_src > 0 ? 100.0 - 100.0 * (double)h.walked / ((double)st->n_src * h.iters) : 0.0);
+#endif
     std::memcpy(out_host->T, h.T, sizeof(h.T));
     out_host->iters = h.iters;
     out_host->converged = h.converged;

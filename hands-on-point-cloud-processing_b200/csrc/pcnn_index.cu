@@ -259,10 +259,10 @@ static int build_impl(pcnn_index** out, int kind, const float* xyz_dev, int64_t 
                 sizeof(unsigned long long) * (size_t)(n0 + 1) + sizeof(float4) * 2 * nboxes + 32;
     v.pts = ix->pts; v.gcode = ix->gcode; v.box = ix->box; v.cube = ix->cube;
 
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    PCNN_BUILD_CUDA(cudaEventCreate(&e0));
-    PCNN_BUILD_CUDA(cudaEventCreate(&e1));
-    PCNN_BUILD_CUDA(cudaEventRecord(e0, s));
+    // owned by the handle from the moment they exist, so free_index destroys them on every error path
+    PCNN_BUILD_CUDA(cudaEventCreate(&ix->ev_begin));
+    PCNN_BUILD_CUDA(cudaEventCreate(&ix->ev_end));
+    PCNN_BUILD_CUDA(cudaEventRecord(ix->ev_begin, s));
     // padding points of the last partial group are never read (count-guarded) but keep them defined
     PCNN_BUILD_CUDA(cudaMemsetAsync(ix->pts, 0xff, sizeof(float4) * (size_t)(n0 * PCNN_GROUP + PCNN_GROUP), s));
     if (ni > 0) {
@@ -296,11 +296,10 @@ static int build_impl(pcnn_index** out, int kind, const float* xyz_dev, int64_t 
         PCNN_BUILD_CUDA(cudaMemsetAsync(ix->cube, 0, sizeof(float) * 12, s));
         PCNN_BUILD_CUDA(cudaMemsetAsync(ix->box, 0, sizeof(float4) * 2, s));
     }
-    PCNN_BUILD_CUDA(cudaEventRecord(e1, s));
-    // The handle is usable by later work on the same stream immediately; build_ms needs the
-    // events to have completed, so it is resolved lazily in pcnn_index_get_info.
-    ix->ev_begin = e0;
-    ix->ev_end = e1;
+    PCNN_BUILD_CUDA(cudaEventRecord(ix->ev_end, s));
+    // The handle is usable by later work on the same stream immediately; work on any OTHER stream
+    // (the host-pointer entry points run on internal streams) first waits for ev_end: wait_build().
+    // build_ms needs the events to have completed, so it is resolved lazily in pcnn_index_get_info.
     ix->build_ms = -1.f;
 #undef PCNN_BUILD_CUDA
     *out = ix;
@@ -438,6 +437,9 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
             PCNN_CUDA(cudaEventCreate(&index->prof1));
         }
         index->opt_profile = value;
+    } else if (!std::strcmp(name, "icp_certificates")) {
+        PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: icp_certificates must be 0 or 1");
+        index->opt_icp_cert = value;
     } else if (!std::strcmp(name, "leaf_log")) {
         PCNN_CHECK_ARG(value >= 0 && value <= 6, "pcnn_set_option: leaf_log must be 0..6");
         index->opt_leaf_log = value;

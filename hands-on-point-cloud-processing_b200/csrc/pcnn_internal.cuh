@@ -39,6 +39,7 @@ struct pcnn_index {
     int opt_coherent_budget2 = 600;  // ... and after the re-seed before it hands its queries over; 0 = never
     unsigned long long* dbg_warp_times = nullptr;  // diagnostics (pcnn_debug_warp_times)
     int opt_profile = 0;
+    int opt_icp_cert = 1;       // ICP correspondence certificates (pcnn_icp.cu); 0 = search every point every iteration
     cudaEvent_t prof0 = nullptr, prof1 = nullptr;  // bracket the last main search kernel
     // staging state of the host-pointer entry points (streams + device buffers), created on
     // first use and kept for the life of the handle so a call costs no allocation
@@ -101,12 +102,14 @@ cudaMemPool_t lib_pool();
 // Stream-ordered scratch allocation that is returned to the pool on scope exit.
 struct Scratch {
     cudaStream_t s;
-    void* p[16];
+    void* p[24];
     int np = 0;
     explicit Scratch(cudaStream_t s_) : s(s_) {}
     template <typename T>
     cudaError_t get(T** out, size_t count) {
         void* q = nullptr;
+        *out = nullptr;
+        if (np >= (int)(sizeof(p) / sizeof(p[0]))) return cudaErrorMemoryAllocation;  // table full: refuse, never overrun
         cudaMemPool_t pool = lib_pool();
         cudaError_t e = pool ? cudaMallocFromPoolAsync(&q, count * sizeof(T) + 16, pool, s)
                              : cudaMallocAsync(&q, count * sizeof(T) + 16, s);
@@ -138,6 +141,13 @@ struct DevBuf {
 };
 
 void free_host_pipe(HostPipe* hp);
+
+// Ordering contract of the handle (pcnn.h): pcnn_index_build only ENQUEUES the build on the caller's
+// stream.  Work enqueued later on that same stream is ordered by the stream; every entry point that
+// runs on a stream of its own (the *_host forms) makes that stream wait for the build first.
+inline cudaError_t wait_build(const pcnn_index* ix, cudaStream_t s) {
+    return ix->ev_end ? cudaStreamWaitEvent(s, ix->ev_end, 0) : cudaSuccess;
+}
 
 // profile brackets: no-ops unless option "profile" is set
 inline void prof_begin(const pcnn_index* ix, cudaStream_t s) {

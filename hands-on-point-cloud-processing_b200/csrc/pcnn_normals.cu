@@ -135,6 +135,7 @@ extern "C" int pcnn_estimate_normals_host(const pcnn_index* index, int max_nn, d
     if (index->n == 0) return PCNN_OK;
     cudaStream_t s = nullptr;
     PCNN_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    wait_build(index, s);
     int rc = PCNN_OK;
     {
         Scratch sc(s);

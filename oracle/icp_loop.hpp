@@ -157,6 +157,20 @@ inline bool solve6(const double N[36], const double g[6], double x[6]) {
     return true;
 }
 
+// Optional record of the small dense systems the loop hands to svd3 / solve6, one row of 64
+// doubles per executed iteration, so a test can give the SAME matrices to LAPACK
+// (numpy.linalg.svd / solve) and check this stand-in for Eigen independently of the end pose:
+//   p2p     [0..8] H  [9..17] U  [18..20] s  [21..29] V  [30..38] R_delta (double, after the det repair)
+//   p2plane [0..35] N = A^T A  [36..41] g = A^T b  [42..47] x  [48] ok
+struct Trace {
+    double* rows = nullptr;
+    int cap = 0, n = 0;
+};
+inline Trace*& trace_slot() {
+    static thread_local Trace* t = nullptr;
+    return t;
+}
+
 template <class F>
 inline void parallel_for(int64_t n, int nthreads, F f) {
     if (nthreads <= 1 || n < 2) { f(0, n); return; }
@@ -266,6 +280,13 @@ Result run(const NN& nn, const float* src, int64_t n_src, const float* tar, int6
                         Rd[r * 3 + c] = V[r * 3 + 0] * B[0] * U[c * 3 + 0] + V[r * 3 + 1] * B[1] * U[c * 3 + 1] +
                                         V[r * 3 + 2] * B[2] * U[c * 3 + 2];
             }
+            if (Trace* tr = trace_slot())
+                if (tr->n < tr->cap) {
+                    double* w = tr->rows + 64 * (size_t)tr->n++;
+                    std::memset(w, 0, 64 * sizeof(double));
+                    std::memcpy(w, H, sizeof(H)); std::memcpy(w + 9, U, sizeof(U)); std::memcpy(w + 18, s, sizeof(s));
+                    std::memcpy(w + 21, V, sizeof(V)); std::memcpy(w + 30, Rd, sizeof(Rd));
+                }
             for (int a = 0; a < 9; a++) R[a] = (float)Rd[a];
             for (int r = 0; r < 3; r++) {
                 if (prm.accum == 0) {
@@ -307,6 +328,13 @@ Result run(const NN& nn, const float* src, int64_t n_src, const float* tar, int6
             }
             double x[6] = {0};
             ok = M > 0 && solve6(N, g, x);  // x = (A^T A)^-1 A^T b, :818
+            if (Trace* tr = trace_slot())
+                if (tr->n < tr->cap) {
+                    double* w = tr->rows + 64 * (size_t)tr->n++;
+                    std::memset(w, 0, 64 * sizeof(double));
+                    std::memcpy(w, N, sizeof(N)); std::memcpy(w + 36, g, sizeof(g)); std::memcpy(w + 42, x, sizeof(x));
+                    w[48] = ok ? 1.0 : 0.0;
+                }
             if (ok) {
                 double xNx = 0, xg = 0;
                 for (int r = 0; r < 6; r++) {

@@ -109,6 +109,20 @@ int pcport_icp(const float* src, int64_t n_src, const float* tar, int64_t n_tar,
     return 0;
 }
 
+// The oracle's own stand-ins for Eigen (JacobiSVD<Matrix3f>, 6x6 inverse), exposed so a test can
+// compare them with LAPACK directly, and the per-iteration record of what the loop gave them:
+// rows [cap][64] doubles (layout: icp_loop.hpp Trace); set before pcport_icp on the same thread,
+// pcport_icp_trace(NULL, 0) returns the number of rows written and switches the record off.
+void pcport_svd3(const double* A, double* U, double* s, double* V) { icp_oracle::svd3(A, U, s, V); }
+int pcport_solve6(const double* N, const double* g, double* x) { return icp_oracle::solve6(N, g, x) ? 1 : 0; }
+int pcport_icp_trace(double* rows, int cap) {
+    static thread_local icp_oracle::Trace tr;
+    const int written = tr.n;
+    tr.rows = rows; tr.cap = rows ? cap : 0; tr.n = 0;
+    icp_oracle::trace_slot() = rows ? &tr : nullptr;
+    return written;
+}
+
 // Exact float32 1-NN of every query (same key as above); used to check the CUDA 1-NN alone.
 int pcport_nn1(const float* tar, int64_t n_tar, const float* q, int64_t nq, int32_t* out_idx,
                float* out_d2, int nthreads) {

@@ -73,6 +73,11 @@ def golden_iss():
 
 
 @pytest.fixture(scope="session")
+def golden_normals():
+    return np.load(os.path.join(GOLDEN, "golden_normals.npz"))
+
+
+@pytest.fixture(scope="session")
 def golden_icp():
     return np.load(os.path.join(GOLDEN, "golden_icp.npz"))
 

@@ -53,12 +53,21 @@ def assert_knn_equals_canonical(idx, dist, can_idx, can_d2):
 
 
 def csr_rows_sorted(off, idx, dist=None):
-    """Sort every CSR row by index; returns (idx_sorted, dist_sorted)."""
+    """Sort every CSR row by index; returns (idx_sorted, dist_sorted).  One argsort of a combined
+    (row, index) key: rows hold distinct indices, so the key is unique."""
     off = np.asarray(off)
     idx = np.asarray(idx)
-    row = np.repeat(np.arange(len(off) - 1), np.diff(off))
-    order = np.lexsort((idx, row))
-    return idx[order], (None if dist is None else np.asarray(dist)[order])
+    if idx.size == 0:
+        return idx, (None if dist is None else np.asarray(dist))
+    key = np.repeat(np.arange(len(off) - 1, dtype=np.int64), np.diff(off))
+    key *= int(idx.max()) + 1
+    key += idx
+    if dist is None:
+        key.sort()
+        key %= int(idx.max()) + 1
+        return key.astype(idx.dtype), None
+    order = np.argsort(key)
+    return idx[order], np.asarray(dist)[order]
 
 
 def assert_radius_matches_reference(off, idx, dist, ref_off, ref_idx, ref_dist):

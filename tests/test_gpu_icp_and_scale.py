@@ -121,7 +121,7 @@ def test_icp_split_phase_equals_fused(pair):
 
 
 @pytest.mark.parametrize("mode", [0, 1])
-def test_icp_certificates_change_nothing_but_the_work(pair, mode, monkeypatch):
+def test_icp_certificates_change_nothing_but_the_work(pair, mode):
     """Correspondence certificates (pcnn_icp.cu: a point whose nearest neighbour provably cannot
     have changed is not searched again) must leave every bit of the result alone: same pose, pairs
     and loss with them switched off, and the number of searches per iteration must fall once the
@@ -131,9 +131,9 @@ def test_icp_certificates_change_nothing_but_the_work(pair, mode, monkeypatch):
     ix = pc.Index(tar)
     dn, ds = torch.from_numpy(nrm).cuda(), torch.from_numpy(src).cuda()
     on = ix.icp(ds, tar_normals=dn, max_iter=40, mode=mode)
-    monkeypatch.setenv("PCNN_ICP_CERT", "0")     # developer switch, read when the state is created
+    ix.set_option("icp_certificates", 0)         # read when the state is created
     off = ix.icp(ds, tar_normals=dn, max_iter=40, mode=mode)
-    monkeypatch.delenv("PCNN_ICP_CERT")
+    ix.set_option("icp_certificates", 1)
     assert off["searches"] == len(src)
     assert np.array_equal(on["T"], off["T"]) and on["pairs"] == off["pairs"] and on["loss"] == off["loss"]
     assert on["iters"] == off["iters"] == 40

@@ -1,7 +1,9 @@
 """GPU parity tests for the PCA normals, through the C ABI
-(pcnn_estimate_normals / _host) against the numpy restatement of pca_normal.py:85-101
-(oracle/pcoracle.py pca_normals).  open3d is absent: the neighbour search of the restatement is
-the oracle's exact brute-force kNN (unpinned by the reference).
+(pcnn_estimate_normals / _host) against (i) tests/golden/golden_normals.npz -- normals computed by
+the reference's OWN PCA() (pca_normal.py:17-33, executed from its source text by
+tests/golden/make_golden_normals.py) on the reference's chair cloud: the PCA step is PINNED -- and
+(ii) the numpy restatement of the loop :85-101 (oracle/pcoracle.py pca_normals) on synthetic scans.
+open3d is absent: the neighbour lists are the oracle's exact brute-force kNN within the radius.
 
 Bar: where the two smallest eigenvalues are separated, |n_gpu . n_ref| >= 1 - 1e-6 (sign is
 arbitrary on both sides); unit length; exactly zero where fewer than 3 neighbours are in range."""
@@ -23,6 +25,39 @@ def _check(normals, ref, ev):
     dots = np.abs((normals[sep].astype(np.float64) * ref[sep]).sum(1))
     assert sep.sum() > 0.9 * nz.sum()
     assert dots.min() >= 1 - 1e-6, (dots.min(), np.argmin(dots))
+
+
+@pytest.mark.parametrize("which", ["", "_r5"])
+def test_normals_against_reference_pca_fixture(golden_iss, golden_normals, which):
+    """CUDA normals vs what the reference's own PCA() returned for the same neighbour lists."""
+    g = golden_normals
+    pts = golden_iss["pts"]
+    ix = pc.Index(pts)
+    try:
+        normals = ix.estimate_normals(max_nn=int(g["max_nn"]), radius=float(g["radius" + which]))
+        if which == "":
+            # the neighbour lists the fixture was made from are the ones the GPU kNN finds
+            idx, dist = ix.knn(pts, int(g["max_nn"]), dist="f64")
+            mine = np.where(dist <= float(g["radius"]), idx, -1)
+            assert np.array_equal(np.sort(mine, 1), np.sort(g["nbr_idx"], 1))
+    finally:
+        ix.close()
+    ref = g["normals" + which]
+    zero = (ref == 0).all(1)
+    assert np.array_equal((normals == 0).all(1), zero) and (zero.sum() == 67 if which == "" else zero.sum() == 0)
+    nz = ~zero
+    assert np.allclose(np.linalg.norm(normals[nz], axis=1), 1.0, atol=1e-6)
+    if which == "":
+        ev = g["evals"]   # descending: [2] is the smallest
+        sep = nz & ((ev[:, 1] - ev[:, 2]) > 1e-6 * np.maximum(ev[:, 0], 1e-300))
+    else:
+        sep = nz
+    dots = np.abs((normals[sep].astype(np.float64) * ref[sep]).sum(1))
+    assert sep.sum() > 0.9 * nz.sum()
+    if which == "":
+        assert dots.min() >= 1 - 1e-6, (dots.min(), int(np.argmin(dots)))
+    else:
+        assert np.quantile(dots, 0.001) >= 1 - 1e-6   # no eigenvalues stored for this set: near-degenerate rows may differ
 
 
 def test_normals_reference_cloud(golden_iss, oracle_port):

@@ -103,6 +103,22 @@ def hostsim():
     return L
 
 
+def _build_compat(tmp_path_factory, name):
+    out = str(tmp_path_factory.mktemp(name) / name)
+    pkg = os.path.join(ROOT, "hands-on-point-cloud-processing_b200")
+    subprocess.check_call(["g++", "-std=c++14", "-O2", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "compat", name + ".cpp"), "-o", out,
+                           "-L" + pkg, "-lpcnn", "-Wl,-rpath," + pkg])
+    return out
+
+
+@pytest.fixture(scope="session")
+def registration_binary(tmp_path_factory):
+    """tests/compat/registration_main.cpp (a caller in the style of Homework9's main.cpp) built against
+    include/pcnn_registration_compat.hpp with mock Eigen / PCL types, linked with libpcnn.so."""
+    return _build_compat(tmp_path_factory, "registration_main")
+
+
 @pytest.fixture(scope="session")
 def compat_binary(tmp_path_factory):
     """tests/compat/compat_main.cpp (a caller in the reference's own style) built against

@@ -202,3 +202,34 @@ def test_certificates_bit_identical_1m_pair(scans1m):
         off = ix.icp(ds, tar_normals=dn, max_iter=30, mode=mode)
         assert _same(on, off), (mode, on, off)
     ix.close()
+
+
+# ------------------------------------------------------------------ the Registration-named boundary
+def test_registration_shim_through_cpp_caller(registration_binary, oracle_port, tmp_path):
+    """include/pcnn_registration_compat.hpp: a C++ caller in the reference's style (setICPparams,
+    ICPpoint2point / ICPpoint2plane with the reference's argument lists, mock Eigen / PCL types)
+    runs through the C ABI and returns the pose the Python entry returns, within 1e-5 of the oracle."""
+    import subprocess
+    src, tar, nrm, T = pc.synth.icp_pair(20_000, seed=pc.synth.BASE_SEED + 3)
+    for name, a in (("src", src), ("tar", tar), ("nrm", nrm)):
+        np.ascontiguousarray(a, np.float32).tofile(str(tmp_path / (name + ".f32")))
+    out = subprocess.run([registration_binary, str(tmp_path / "src.f32"), str(tmp_path / "tar.f32"),
+                          str(tmp_path / "nrm.f32"), "30", "1.0"], capture_output=True, text=True, check=True).stdout
+    rows = {ln.split(":")[0]: ln.split(":")[1].split() for ln in out.strip().splitlines()}
+    ix = pc.Index(tar)
+    for mode, key in ((0, "p2p"), (1, "p2plane")):
+        v = rows[key]
+        R = np.array([float(x) for x in v[:9]], np.float32).reshape(3, 3)
+        t = np.array([float(x) for x in v[9:12]], np.float32)
+        assert v[12:] == ["iters", "30", "pairs", v[15], "status", "0"]
+        got = ix.icp(src, tar_normals=nrm, max_iter=30, max_corres_dist=1.0, mode=mode)
+        assert np.array_equal(R, got["T"][:3, :3]) and np.array_equal(t, got["T"][:3, 3]) and int(v[15]) == got["pairs"]
+        want = oracle_port.icp(src, tar, nrm, max_iter=30, max_corres_dist=1.0, mode=mode, accum=1, nthreads=8)
+        assert np.abs(R - want["T"][:3, :3]).max() < POSE_TOL and np.abs(t - want["T"][:3, 3]).max() < POSE_TOL
+    # transformCloudInplace of the shim = the reference's float32 operation order
+    m = np.array([float(x) for x in rows["moved0"]], np.float32)
+    x = src[0]
+    exp = np.array([np.float32(np.float32(np.float32(R[r, 0] * x[0]) + np.float32(R[r, 1] * x[1])) + np.float32(R[r, 2] * x[2])) + t[r]
+                    for r in range(3)], np.float32)
+    assert np.allclose(m, exp, rtol=0, atol=1e-6)
+    ix.close()

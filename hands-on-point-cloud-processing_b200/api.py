@@ -79,6 +79,7 @@ EXPORTS = [
     "pcnn_voxel_downsample", "pcnn_estimate_normals", "pcnn_estimate_normals_host",
     "pcnn_desc_nn1", "pcnn_match_descriptors", "pcnn_ransac",
     "pcnn_icp_peer_export", "pcnn_icp_peer_attach", "pcnn_icp_step_peer", "pcnn_icp_peer_detach",
+    "pcnn_radius_count_noalloc",
 ]
 
 
@@ -106,6 +107,7 @@ def lib():
     L.pcnn_get_profile.argtypes = [vp, C.POINTER(C.c_float)]
     L.pcnn_radius_count.argtypes = [vp, vp, i64, i32, f64, vp, C.POINTER(i64), vp]
     L.pcnn_radius_fill.argtypes = [vp, vp, i64, i32, f64, vp, vp, vp, vp, vp]
+    L.pcnn_radius_count_noalloc.argtypes = [vp, vp, i64, i32, f64, vp, vp]
     L.pcnn_radius_host.argtypes = [vp, vp, i64, i32, f64, vp, vp, vp, vp, i64]
     L.pcnn_icp.argtypes = [vp, vp, vp, i64, i32, vp, C.POINTER(IcpParams), C.POINTER(IcpResult), vp]
     L.pcnn_icp_host.argtypes = [vp, vp, vp, i64, i32, vp, C.POINTER(IcpParams), C.POINTER(IcpResult)]

@@ -772,3 +772,95 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
 }
 
 }  // namespace pcnn
+
+// ------------------------------------------------------------------ allocation-free count pass
+// pcnn_radius_count_noalloc (include/pcnn.h): the count pass of the radius search for callers that
+// cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Same
+// kernels as pcnn_radius_count on a sparse batch in the caller's query order (radius_stack_kernel,
+// then the tiled scan); what differs is where the scratch lives: the per-query counts and the
+// scan's tile sums sit in ONE file-scope device array instead of the stream-ordered pool.  Every
+// GPU that loads the library holds the array until exit.  All calls share it and it keeps the last
+// call's contents; every word this call reads it has written first (counts[0, nq) by the count
+// kernel, the tile sums by the scan), so nothing needs clearing -- but two calls that overlap on
+// the GPU (different streams, no ordering between them) race on it.
+namespace pcnn {
+constexpr size_t NOALLOC_COUNT_BYTES = ((size_t)PCNN_NOALLOC_MAX_QUERIES + 1) * sizeof(long long);
+constexpr size_t NOALLOC_TILES = ((size_t)PCNN_NOALLOC_MAX_QUERIES + SCAN_TILE - 1) / SCAN_TILE + 1;
+constexpr size_t NOALLOC_BYTES = ((NOALLOC_COUNT_BYTES + 255) / 256) * 256 + NOALLOC_TILES * sizeof(long long);
+static_assert(NOALLOC_BYTES <= (size_t)PCNN_NOALLOC_SCRATCH_BYTES, "pcnn.h states the size of the scratch array");
+}  // namespace pcnn
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PCNN_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address a
+// kernel may use comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) {
+        pcnn::set_error("pcnn_radius_count_noalloc: device %d out of range", device);
+        return PCNN_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);  // the caller made `device` current
+        if (e != cudaSuccess || !p) {
+            pcnn::set_error("pcnn_radius_count_noalloc: cudaGetSymbolAddress failed on device %d: %s", device,
+                            cudaGetErrorString(e));
+            return PCNN_ERR_CUDA;
+        }
+        g_noalloc_ptr[device] = p;
+    }
+    *out = static_cast<unsigned char*>(g_noalloc_ptr[device]);
+    return PCNN_OK;
+}
+}  // namespace
+
+extern "C" int pcnn_radius_count_noalloc(const pcnn_index* index, const float* q_dev, int64_t nq, int stride,
+                                         double radius, int64_t* out_offsets_dev, pcnn_stream stream) {
+    using namespace pcnn;
+    PCNN_CHECK_ARG(index != nullptr, "pcnn_radius_count_noalloc: index is NULL");
+    PCNN_CHECK_ARG(nq >= 0, "pcnn_radius_count_noalloc: nq=%lld is negative", (long long)nq);
+    PCNN_CHECK_ARG(stride >= 3, "pcnn_radius_count_noalloc: stride must be >= 3 floats (got %d)", stride);
+    PCNN_CHECK_ARG(nq == 0 || q_dev != nullptr, "pcnn_radius_count_noalloc: query pointer is NULL");
+    PCNN_CHECK_ARG(out_offsets_dev != nullptr, "pcnn_radius_count_noalloc: out_offsets is NULL");
+    PCNN_CHECK_ARG(radius == radius, "pcnn_radius_count_noalloc: radius is NaN");
+    if (nq > (int64_t)PCNN_NOALLOC_MAX_QUERIES) {
+        set_error("pcnn_radius_count_noalloc: nq=%lld exceeds PCNN_NOALLOC_MAX_QUERIES=%d (the scratch is a fixed "
+                  "%d-byte device array); split the batch or use pcnn_radius_count",
+                  (long long)nq, PCNN_NOALLOC_MAX_QUERIES, PCNN_NOALLOC_SCRATCH_BYTES);
+        return PCNN_ERR_UNSUPPORTED;
+    }
+    if (index->view.n0 >= RL_MAX_GROUPS) {
+        set_error("pcnn_radius_count_noalloc: clouds of 2^30 points and more are not served by this entry point");
+        return PCNN_ERR_UNSUPPORTED;
+    }
+    DeviceGuard g(index->device);
+    if (!g.ok) {
+        set_error("pcnn_radius_count_noalloc: cannot select CUDA device %d (no CPU fallback exists)", index->device);
+        return PCNN_ERR_CUDA;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (nq == 0) {
+        PCNN_CUDA(cudaMemsetAsync(out_offsets_dev, 0, sizeof(int64_t), s));
+        return PCNN_OK;
+    }
+    unsigned char* base = nullptr;
+    if (int rc = noalloc_scratch(index->device, &base)) return rc;
+    long long* counts = reinterpret_cast<long long*>(base);
+    long long* tile_sums = reinterpret_cast<long long*>(base + ((NOALLOC_COUNT_BYTES + 255) / 256) * 256);
+    const int n = (int)nq;
+    const RadiusThr rt = make_thr(radius);
+    radius_stack_kernel<false, false><<<(n + RK_WARPS - 1) / RK_WARPS, RK_WARPS * 32, 0, s>>>(
+        index->view, q_dev, n, stride, nullptr, rt, counts, nullptr, nullptr, nullptr, nullptr);
+    const int ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    scan_tiles_kernel<<<ntiles, 1024, 0, s>>>(counts, n, (long long*)out_offsets_dev, tile_sums);
+    scan_sums_kernel<<<1, 1024, 0, s>>>(tile_sums, ntiles);
+    scan_add_kernel<<<ntiles, 1024, 0, s>>>((long long*)out_offsets_dev, n, tile_sums, ntiles);
+    PCNN_CUDA(cudaGetLastError());
+    return PCNN_OK;
+}
+

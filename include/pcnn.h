@@ -170,6 +170,26 @@ int pcnn_radius_host(const pcnn_index* index, const float* q_host, int64_t nq, i
                      double radius, int64_t* offsets_host, int32_t* out_idx_host,
                      float* out_dist_host, double* out_dist64_host, int64_t capacity);
 
+/* Allocation-free count pass.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same result as pcnn_radius_count -- out_offsets_dev[nq+1], the
+ * exclusive scan of the per-query hit counts, bit for bit -- but the call allocates NOTHING: no
+ * cudaMalloc / cudaFree, no stream-ordered pool, no library routine that allocates.  Its scratch
+ * (per-query counts, scan tile sums) is a file-scope device array of PCNN_NOALLOC_SCRATCH_BYTES that
+ * every GPU which loads the library holds until exit.  Limits and rules:
+ *   - nq <= PCNN_NOALLOC_MAX_QUERIES, otherwise PCNN_ERR_UNSUPPORTED (split the batch);
+ *   - queries are processed in the caller's order (no query ordering: that needs scratch of its own),
+ *     one warp per query; meant for small and medium batches;
+ *   - all calls share the one array and it keeps the last call's contents (every word a call reads it
+ *     has written first, nothing needs clearing): calls that OVERLAP on the GPU -- different streams
+ *     without an ordering between them, on the same device -- race on it.  Calls on one stream, or
+ *     ordered by events, are safe; different devices have separate copies;
+ *   - only enqueues on `stream`; the total is out_offsets_dev[nq] once the stream has passed it. */
+#define PCNN_NOALLOC_MAX_QUERIES 262144
+#define PCNN_NOALLOC_SCRATCH_BYTES (2 * 1024 * 1024 + 4096)
+int pcnn_radius_count_noalloc(const pcnn_index* index, const float* q_dev, int64_t nq, int stride,
+                              double radius, int64_t* out_offsets_dev, pcnn_stream stream);
+
 /* ------------------------------------------------------------------ ICP
  * Replaces Registration::ICPpoint2point (registration.cpp:862-1011) and ICPpoint2plane
  * (:710-859) minus the normal-space sampling done before the loop (:728-729, :880-881):

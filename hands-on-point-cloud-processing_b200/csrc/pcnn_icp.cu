@@ -52,6 +52,8 @@ namespace pcnn {
 
 constexpr int ICP_THREADS = 128;
 constexpr int ICP_NS = PCNN_ICP_NSUMS;  // 32
+constexpr int ICP_FOLD_G = 16;     // partial rows folded by the last block of each group of 16 blocks ...
+constexpr int ICP_MAX_GROUPS = 128; // ... and the group rows by the last group to finish (grids of up to 2048 blocks)
 // sums layout: p2p  [0..2]=sum p  [3..5]=sum q  [6..14]=sum q_r*p_c  [28]=count
 //              p2pl [0..20]=upper triangle of A^T A  [21..26]=A^T b  [27]=b^T b  [28]=count
 //              [31] (as int64) = (global index of the last kept pair << 32) | float bits of its d2
@@ -71,6 +73,7 @@ struct Dev {
     float loss;
     long long last_pairs;
     unsigned block_counter;
+    unsigned group_counter[pcnn::ICP_MAX_GROUPS];  // two-level fold: blocks of a group that have written their partial row
     unsigned long long peer_seq;  // iterations exchanged so far (identical on every rank)
     unsigned long long walked;    // searches run so far (the rest were certified); PCNN_ICP_STATS prints it
     unsigned long long walked_mark;
@@ -99,36 +102,43 @@ __device__ __forceinline__ void xform(const float* R, const float* t, float& x, 
 }
 
 __device__ bool chol6_dev(const double* N, const double* g, double* x) {
-    double L[36];
+    // One thread solves the 6x6 system once per iteration, so its LATENCY is on every iteration's
+    // critical path: one square root and one reciprocal per pivot, every other division a multiply
+    // (6 + 6 slow operations instead of 6 + 33; 6.5 us -> see DESIGN 4.5).
+    double L[36], inv[6];
 #pragma unroll
     for (int i = 0; i < 36; i++) L[i] = 0;
 #pragma unroll
-    for (int i = 0; i < 6; i++)
+    for (int j = 0; j < 6; j++) {
+        double d = N[j * 6 + j];
 #pragma unroll
-        for (int j = 0; j <= i; j++) {
+        for (int k = 0; k < j; k++) d -= L[j * 6 + k] * L[j * 6 + k];
+        if (!(d > 0)) return false;
+        const double r = sqrt(d);
+        L[j * 6 + j] = r;
+        inv[j] = 1.0 / r;
+#pragma unroll
+        for (int i = j + 1; i < 6; i++) {
             double s = N[i * 6 + j];
 #pragma unroll
             for (int k = 0; k < j; k++) s -= L[i * 6 + k] * L[j * 6 + k];
-            if (i == j) {
-                if (!(s > 0)) return false;
-                L[i * 6 + i] = sqrt(s);
-            } else
-                L[i * 6 + j] = s / L[j * 6 + j];
+            L[i * 6 + j] = s * inv[j];
         }
+    }
     double y[6];
 #pragma unroll
     for (int i = 0; i < 6; i++) {
         double s = g[i];
 #pragma unroll
         for (int k = 0; k < i; k++) s -= L[i * 6 + k] * y[k];
-        y[i] = s / L[i * 6 + i];
+        y[i] = s * inv[i];
     }
 #pragma unroll
     for (int i = 5; i >= 0; i--) {
         double s = y[i];
 #pragma unroll
         for (int k = i + 1; k < 6; k++) s -= L[k * 6 + i] * x[k];
-        x[i] = s / L[i * 6 + i];
+        x[i] = s * inv[i];
     }
     return true;
 }
@@ -578,35 +588,83 @@ icp_accumulate_kernel(IndexView iv, const float4* cur, const float4* __restrict_
         }
         partials[(size_t)blockIdx.x * ICP_NS + slot] = s;
     }
-    // last-block-done: fold the per-block partials in a fixed order
+    // Two-level fold in a fixed order (deterministic whatever the timing; no floating atomics): the
+    // last block of every group of ICP_FOLD_G blocks to arrive folds that group's partial rows into
+    // one group row, and the last GROUP to finish folds the group rows.  One block folding all rows
+    // (up to 296 x 32 doubles, five rounds of dependent L2 loads) took 16 us of every iteration.
 #ifdef PCNN_ICP_TIMING
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_b));
 #endif
+    const int nb = (int)gridDim.x;
+    const int ngroups = (nb + ICP_FOLD_G - 1) / ICP_FOLD_G;
+    const int grp = blockIdx.x / ICP_FOLD_G;
+    const int gfirst = grp * ICP_FOLD_G, gsize = min(ICP_FOLD_G, nb - gfirst);
+    double* const grows = partials + (size_t)nb * ICP_NS;  // [ngroups][32] behind the per-block rows
+    const int col = threadIdx.x & 31, part = threadIdx.x >> 5;
+    constexpr int P4 = ICP_THREADS / 32;
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
-        const unsigned ticket = atomicAdd(&st->block_counter, 1u);
-        s_is_last = (ticket == gridDim.x - 1);
+        const unsigned ticket = atomicAdd(&st->group_counter[grp], 1u);
+        s_is_last = (ticket == (unsigned)gsize - 1u);
     }
     __syncthreads();
     if (!s_is_last) return;
     __threadfence();
     {
-        const int col = threadIdx.x & 31, part = threadIdx.x >> 5;  // 4 row-strided partial sums per column
-        // fixed order whatever the timing: 8 interleaved accumulators per (column, part), then a
-        // fixed tree; the loads of one batch are independent so they overlap
-        constexpr int P4 = ICP_THREADS / 32, UN = 16;
+        // level 1: <= 16 rows, four per (column, part), loads independent
+        double x[ICP_FOLD_G / P4];
+#pragma unroll
+        for (int u = 0; u < ICP_FOLD_G / P4; u++) {
+            const int r = part + u * P4;
+            x[u] = r < gsize ? __ldcg(partials + (size_t)(gfirst + r) * ICP_NS + col) : (col == 31 ? __longlong_as_double(-1LL) : 0.0);
+        }
+        double sacc;
+        if (col == 31) {
+            long long m = -1;
+#pragma unroll
+            for (int u = 0; u < ICP_FOLD_G / P4; u++) { const long long xi = __double_as_longlong(x[u]); m = xi > m ? xi : m; }
+            sacc = __longlong_as_double(m);
+        } else {
+            sacc = (x[0] + x[1]) + (x[2] + x[3]);
+        }
+        s_part[part][col] = sacc;
+    }
+    __syncthreads();
+    if (threadIdx.x < ICP_NS) {
+        double r;
+        if (col == 31) {
+            long long m = __double_as_longlong(s_part[0][col]);
+            for (int p2 = 1; p2 < P4; p2++) { const long long xi = __double_as_longlong(s_part[p2][col]); m = xi > m ? xi : m; }
+            r = __longlong_as_double(m);
+        } else {
+            r = ((s_part[0][col] + s_part[1][col]) + s_part[2][col]) + s_part[3][col];
+        }
+        grows[(size_t)grp * ICP_NS + col] = r;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        st->group_counter[grp] = 0;  // for the next launch on this state
+        const unsigned ticket = atomicAdd(&st->block_counter, 1u);
+        s_is_last = (ticket == (unsigned)ngroups - 1u);
+    }
+    __syncthreads();
+    if (!s_is_last) return;
+    __threadfence();
+    {
+        // level 2: the group rows (<= ICP_MAX_GROUPS), eight interleaved accumulators per (column, part)
+        constexpr int UN = 8;
         double acc[UN];
         long long mm[UN];
 #pragma unroll
         for (int u = 0; u < UN; u++) { acc[u] = 0.0; mm[u] = -1; }
-        const int nb = (int)gridDim.x;
-        for (int b0 = part; b0 < nb; b0 += P4 * UN) {
+        for (int b0 = part; b0 < ngroups; b0 += P4 * UN) {
             double x[UN];
 #pragma unroll
             for (int u = 0; u < UN; u++) {
                 const int b = b0 + u * P4;
-                x[u] = b < nb ? __ldcg(partials + (size_t)b * ICP_NS + col) : (col == 31 ? __longlong_as_double(-1LL) : 0.0);
+                x[u] = b < ngroups ? __ldcg(grows + (size_t)b * ICP_NS + col) : (col == 31 ? __longlong_as_double(-1LL) : 0.0);
             }
 #pragma unroll
             for (int u = 0; u < UN; u++) {
@@ -618,11 +676,11 @@ icp_accumulate_kernel(IndexView iv, const float4* cur, const float4* __restrict_
         for (int w = UN / 2; w > 0; w >>= 1)  // fixed tree
 #pragma unroll
             for (int u = 0; u < w; u++) acc[u] += acc[u + w];
-        const double s = acc[0];
         long long m = -1;
 #pragma unroll
         for (int u = 0; u < UN; u++) m = mm[u] > m ? mm[u] : m;
-        s_part[part][col] = (col == 31) ? __longlong_as_double(m) : s;
+        __syncthreads();  // level 1's readers of s_part are done
+        s_part[part][col] = (col == 31) ? __longlong_as_double(m) : acc[0];
     }
     __syncthreads();
     if (threadIdx.x < ICP_NS) {
@@ -698,6 +756,7 @@ __global__ void icp_state_init_kernel(Dev* st, const float* __restrict__ T0) {
         for (int i = 0; i < ICP_NS; i++) st->sums[i] = 0.0;
         st->iters = 0; st->converged = 0; st->status = 0; st->done = 0; st->unchanged = 0;
         st->last_loss = 0.f; st->loss = 0.f; st->last_pairs = 0; st->block_counter = 0;
+        for (int i = 0; i < ICP_MAX_GROUPS; i++) st->group_counter[i] = 0;
         st->peer_seq = 0;
         st->walked = 0; st->walked_mark = 0; st->last_searches = 0;
     }
@@ -833,6 +892,7 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
 #ifdef PCNN_STUDY
         if (const char* e = getenv("PCNN_ICP_ACC_BLOCKS")) st->acc_blocks = atoi(e) < st->nblocks ? atoi(e) : st->nblocks;
 #endif
+        if (st->acc_blocks > ICP_FOLD_G * ICP_MAX_GROUPS) st->acc_blocks = ICP_FOLD_G * ICP_MAX_GROUPS;
         if (st->acc_blocks < 1) st->acc_blocks = 1;
     }
     st->mem_stream = s;
@@ -847,7 +907,7 @@ int pcnn_icp_create(pcnn_icp_state** out, const pcnn_index* target, const float*
     if (e == cudaSuccess) e = palloc(&st->prev, sizeof(int) * (size_t)(n + 1));
     if (e == cudaSuccess) e = palloc(&st->cert, sizeof(float4) * (size_t)(n + 1));
     if (e == cudaSuccess) e = palloc(&st->prev2, sizeof(int) * (size_t)(n + 1));
-    if (e == cudaSuccess) e = palloc(&st->partials, sizeof(double) * ICP_NS * (size_t)st->nblocks);
+    if (e == cudaSuccess) e = palloc(&st->partials, sizeof(double) * ICP_NS * ((size_t)st->nblocks + ICP_MAX_GROUPS));
     if (e == cudaSuccess) e = palloc(&st->dev, sizeof(Dev));
     if (e == cudaSuccess && params->mode == 1) e = palloc(&st->nrm, sizeof(float4) * (size_t)(target->n + 1));
     if (e != cudaSuccess) {

@@ -43,10 +43,12 @@ namespace {
 // 50 GB/s, and the searches keep just ahead of it); shorter first stages gain nothing because
 // the query ordering of a stage is launch-latency bound (~0.2 ms whatever its size).
 int64_t host_chunk(int64_t nq) {
+#ifdef PCNN_STUDY
     if (const char* e = std::getenv("PCNN_HOST_CHUNK")) {  // tuning aid
         const long long v = std::atoll(e);
         if (v > 0) return std::min<int64_t>(v, nq);
     }
+#endif
     int64_t c = (nq + 7) / 8;
     c = std::max<int64_t>(c, 1 << 16);
     c = std::min<int64_t>(c, 1 << 18);
@@ -114,7 +116,9 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
     if (rc != PCNN_OK) return rc;
     const int64_t chunk = host_chunk(nq);
     int max_streams = HOST_STREAMS;
+#ifdef PCNN_STUDY
     if (const char* ev = std::getenv("PCNN_HOST_STREAMS")) max_streams = std::max(1, std::min(HOST_STREAMS, std::atoi(ev)));  // tuning aid
+#endif
     const int nstreams = (int)std::min<int64_t>(max_streams, (nq + chunk - 1) / chunk);
     cudaError_t e = cudaSuccess;
     for (int i = 0; i < nstreams && e == cudaSuccess; i++) {
@@ -128,7 +132,11 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
         return PCNN_ERR_NOMEM;
     }
     // PCNN_PIPE_TRACE=1 (tuning aid): per-stage event times of this call on stderr
+#ifdef PCNN_STUDY
     static const bool trace = std::getenv("PCNN_PIPE_TRACE") != nullptr;
+#else
+    constexpr bool trace = false;
+#endif
     std::vector<cudaEvent_t> tev;
     std::vector<double> thost;
     const auto t_host0 = std::chrono::steady_clock::now();

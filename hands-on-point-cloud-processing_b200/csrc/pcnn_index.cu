@@ -428,6 +428,13 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
         index->opt_sort_queries = value;
     } else if (!std::strcmp(name, "method")) {
         PCNN_CHECK_ARG(value >= 0 && value <= 10, "pcnn_set_option: method must be 0..10");
+#ifndef PCNN_STUDY
+        if (value != 0 && value != 2 && value != 3 && value != 7 && value != 9) {
+            set_error("pcnn_set_option: kNN method %d is a study variant; this build ships 0 (auto), 2, 3, 7 and 9 "
+                      "(build with -DPCNN_STUDY for the others)", value);
+            return PCNN_ERR_UNSUPPORTED;
+        }
+#endif
         index->opt_method = value;
     } else if (!std::strcmp(name, "profile")) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: profile must be 0 or 1");
@@ -451,6 +458,13 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
         index->opt_coherent_budget = value;
     } else if (!std::strcmp(name, "radius_batch")) {
         PCNN_CHECK_ARG(value >= 0 && value <= 5, "pcnn_set_option: radius_batch must be 0 (warp per query), 1 (auto), 2 (batched runs), 3 (lock-step), 4 (stack walk) or 5 (stack walk, batched runs)");
+#ifndef PCNN_STUDY
+        if (value == 2 || value == 3) {
+            set_error("pcnn_set_option: radius kernel %d is a study variant; this build ships 1 (auto), 0, 4 and 5 "
+                      "(build with -DPCNN_STUDY for the others)", value);
+            return PCNN_ERR_UNSUPPORTED;
+        }
+#endif
         index->opt_radius_batch = value;
     } else if (!std::strcmp(name, "radius_run_div")) {
         PCNN_CHECK_ARG(value >= 0 && value <= 1024, "pcnn_set_option: radius_run_div must be 0 (default per pass) or 1..1024");

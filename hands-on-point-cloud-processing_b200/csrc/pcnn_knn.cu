@@ -102,6 +102,7 @@ __device__ __forceinline__ void write_row(const TopK<K>& tk, int64_t row, int k,
         }
     }
 }
+#ifdef PCNN_STUDY  // measured-slower variant kept for study: not in the shipped library
 
 template <int K>
 __global__ void __launch_bounds__(KT_THREADS)
@@ -313,6 +314,7 @@ knn_coherent_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
     }
 }
 
+#endif  // PCNN_STUDY
 // ------------------------------------------------------------------ shared walk, per-lane scan queues
 // Same shared, warp-uniform walk over the boxes as knn_coherent_kernel, but a lane that needs a
 // group does not make the whole warp scan it: it pushes the group on its own small queue (shared
@@ -356,6 +358,7 @@ __device__ __forceinline__ void scan_own_group(const IndexView& iv, int g, bool 
     }
 }
 
+#ifdef PCNN_STUDY  // measured-slower variant kept for study: not in the shipped library
 template <int K>
 __global__ void __launch_bounds__(KT_THREADS)
 knn_queue_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
@@ -511,6 +514,7 @@ knn_queue_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     }
 }
 
+#endif  // PCNN_STUDY
 // ------------------------------------------------------------------ lock-step per-lane walks
 // Every lane walks the hierarchy for its OWN query (own position, own window, own bound), but
 // the warp executes the walks in lock step: a round is a fixed sequence of predicated box
@@ -523,6 +527,7 @@ knn_queue_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
 // resumes.
 constexpr int KL_WALK = 8;  // box steps per round
 
+#ifdef PCNN_STUDY  // measured-slower variant kept for study: not in the shipped library
 template <int K>
 __global__ void __launch_bounds__(KT_THREADS)
 knn_lockstep_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
@@ -662,6 +667,7 @@ knn_lockstep_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
     }
 }
 
+#endif  // PCNN_STUDY
 // ------------------------------------------------------------------ lock-step nearest-first walks
 // The order of the reference's own search (near child first, kdtree.hpp:347-363), without its
 // recursion: every lane runs a depth-first walk of the binary hierarchy for its own query,
@@ -817,6 +823,7 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     }
 }
 
+#ifdef PCNN_STUDY  // measured-slower variant kept for study: not in the shipped library
 }  // namespace pcnn
 #include "pcnn_knn_refill.cuh"
 namespace pcnn {
@@ -1006,6 +1013,7 @@ knn_hybrid_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     }
 }
 
+#endif  // PCNN_STUDY
 // ------------------------------------------------------------------ nearest-first walks, 16 < k <= 32
 // Same lock-step nearest-first walk as knn_dfs_kernel; the k best of a lane do not fit its
 // registers, so they live in a binary MAX-heap in shared memory (slot-major, one column per
@@ -1437,6 +1445,7 @@ knn_warp_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int nq, 
                  out_dist, out_dist64);
 }
 
+#ifdef PCNN_STUDY  // measured-slower variant kept for study: not in the shipped library
 // Same search for the queries a budgeted kernel gave up on: qlist[0 .. *qcount) holds their
 // ids; a fixed grid of warps walks the list.
 __global__ void __launch_bounds__(WQ_WARPS * 32)
@@ -1455,7 +1464,9 @@ knn_warp_list_kernel(IndexView iv, WarpPlan wp, const float* __restrict__ q, int
     }
 }
 
+#endif  // PCNN_STUDY
 // ------------------------------------------------------------------ launcher
+#ifdef PCNN_STUDY
 template <int K>
 static void launch_thread_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
                             int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
@@ -1485,12 +1496,14 @@ static void launch_lockstep_k(const pcnn_index* ix, const float* q, int nq, int 
         ix->view, q, nq, stride, perm, k, oi, od, od64,
         ix->opt_coherent_budget > 0 ? ix->opt_coherent_budget : 0x7fffffff, ix->dbg_warp_times);
 }
+#endif  // PCNN_STUDY
 template <int K>
 static void launch_dfs_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
                          int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
     knn_dfs_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
         ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
 }
+#ifdef PCNN_STUDY
 template <int K>
 static void launch_refill_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
                             int k, int32_t* oi, float* od, double* od64, unsigned* counter, cudaStream_t s) {
@@ -1503,7 +1516,7 @@ static void launch_refill_k(const pcnn_index* ix, const float* q, int nq, int st
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ix->device);
         blocks = per_sm * sms;
     }
-    static int refill_min = getenv("PCNN_REFILL_MIN") ? atoi(getenv("PCNN_REFILL_MIN")) : PCNN_REFILL_MIN;
+    static int refill_min = getenv("PCNN_REFILL_MIN") ? atoi(getenv("PCNN_REFILL_MIN")) : PCNN_REFILL_MIN;  // study build only
     const int need = (nq + KT_THREADS - 1) / KT_THREADS;
     knn_dfs_refill_kernel<K><<<need < blocks ? need : blocks, KT_THREADS, 0, s>>>(
         ix->view, q, nq, stride, perm, k, oi, od, od64, counter, refill_min);
@@ -1515,6 +1528,7 @@ static void launch_hybrid_k(const pcnn_index* ix, const float* q, int nq, int st
         ix->view, q, nq, stride, perm, k, oi, od, od64,
         ix->opt_coherent_budget > 0 ? ix->opt_coherent_budget : 0x7fffffff, ix->dbg_warp_times);
 }
+#endif  // PCNN_STUDY
 template <int K>
 static void launch_brute_k(const pcnn_index* ix, const float* q, int nq, int stride, int k, int32_t* oi,
                            float* od, double* od64, cudaStream_t s) {
@@ -1527,6 +1541,10 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     if (nq64 == 0) return PCNN_OK;
     const int nq = (int)nq64;
     int method = ix->opt_method;
+#ifndef PCNN_STUDY
+    // the shipped library holds methods 2, 3, 7 and 9 only (pcnn_set_option refuses the others)
+    if (method != 2 && method != 3 && method != 7 && method != 9) method = 0;
+#endif
     if (method == 0) method = (k <= 16) ? 7 : (k <= KH_CAP ? 9 : 2);
     if (method == 9 && (k > KH_CAP || ix->n == 0)) method = 2;
     if ((method == 1 || method == 3 || method == 4 || method == 5 || method == 6 || method == 7 || method == 8 || method == 10) && k > 16) method = 2;
@@ -1543,6 +1561,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         knn_dfs_heap_kernel<<<(nq + KH_THREADS - 1) / KH_THREADS, KH_THREADS, 0, s>>>(
             ix->view, q, nq, stride, perm, k, out_idx, out_dist, out_dist64);
         prof_end(ix, s);
+#ifdef PCNN_STUDY
     } else if (method == 8) {
         Scratch sc(s);
         unsigned* perm = nullptr;
@@ -1574,6 +1593,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         else if (k <= 8) launch_refill_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, counter, s);
         else launch_refill_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, counter, s);
         prof_end(ix, s);
+#endif  // PCNN_STUDY
     } else if (method == 7) {
         Scratch sc(s);
         unsigned* perm = nullptr;
@@ -1589,6 +1609,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         else if (k <= 12) launch_dfs_k<12>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);  // 9..12: pca_normal.py's max_nn = 10
         else launch_dfs_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         prof_end(ix, s);
+#ifdef PCNN_STUDY
     } else if (method == 6) {
         Scratch sc(s);
         unsigned* perm = nullptr;
@@ -1659,6 +1680,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         else if (k <= 8) launch_thread_k<8>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         else launch_thread_k<16>(ix, q, nq, stride, perm, k, out_idx, out_dist, out_dist64, s);
         prof_end(ix, s);
+#endif  // PCNN_STUDY
     } else if (method == 3) {
         prof_begin(ix, s);
         if (k <= 1) launch_brute_k<1>(ix, q, nq, stride, k, out_idx, out_dist, out_dist64, s);

@@ -557,6 +557,9 @@ static RadiusThr make_thr(double radius) {
 enum { RM_WARP = 0, RM_BATCH = 2, RM_LOCKSTEP = 3, RM_STACK = 4, RM_STACK_BATCH = 5 };
 static int radius_method(const pcnn_index* ix, int nq, double radius, bool fill, double hits_per_query) {
     int m = ix->opt_radius_batch;
+#ifndef PCNN_STUDY
+    if (m == RM_BATCH || m == RM_LOCKSTEP) m = 1;  // study variants: not in the shipped library
+#endif
     if (m == 1) {
         const bool dense = ix->opt_sort_queries && nq > 1024 && 2 * (int64_t)nq >= ix->n;
         m = dense ? RM_STACK_BATCH : RM_STACK;
@@ -662,6 +665,7 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
     } else if (method == RM_STACK) {
         radius_stack_kernel<false, false><<<(nq + RK_WARPS - 1) / RK_WARPS, RK_WARPS * 32, 0, s>>>(
             ix->view, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
+#ifdef PCNN_STUDY
     } else if (method == RM_LOCKSTEP) {
         radius_lockstep_kernel<false, false><<<(nq + RL_THREADS - 1) / RL_THREADS, RL_THREADS, 0, s>>>(
             ix->view, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
@@ -670,6 +674,7 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
         radius_batch_kernel<false, false><<<(nwarps + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
             ix->view, wp, q, nq, stride, perm, rt, run_extent(ix, radius, false, false), counts, nullptr, nullptr,
             nullptr, nullptr);
+#endif
     } else {
         radius_warp_kernel<false, false><<<(nq + WQ_WARPS - 1) / WQ_WARPS, WQ_WARPS * 32, 0, s>>>(
             ix->view, wp, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
@@ -730,6 +735,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
         PCNN_CUDA(cudaGetLastError());
         return PCNN_OK;
     }
+#ifdef PCNN_STUDY
     if (method == RM_LOCKSTEP) {
         const int lgrid = (nq + RL_THREADS - 1) / RL_THREADS;
         if (out_dist64)
@@ -758,6 +764,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
         PCNN_CUDA(cudaGetLastError());
         return PCNN_OK;
     }
+#endif  // PCNN_STUDY
     const int grid = (nq + WQ_WARPS - 1) / WQ_WARPS;
     if (out_dist64)
         radius_warp_kernel<true, true><<<grid, WQ_WARPS * 32, 0, s>>>(

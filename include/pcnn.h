@@ -14,8 +14,9 @@
  *   nanoflann 1-NN as ICP uses it               registration.cpp:772-785, :925-941
  *
  * Every entry point below names the reference interface it replaces.  Plain pointers and
- * sizes only; no C++ or torch types.  hands-on-point-cloud-processing_b200/compat/pcnn_compat.hpp
- * restores the reference's own names on top of this header.
+ * sizes only; no C++ or torch types.  include/pcnn_compat.hpp (Homework2 names) and
+ * include/pcnn_registration_compat.hpp (Homework9's Registration) restore the reference's own names
+ * on top of this header.
  *
  * Conventions
  *  - All functions return an int status: PCNN_OK (0) or a negative PCNN_ERR_*; the message
@@ -126,18 +127,21 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
 
 /* Query-side knobs (all have working defaults).  `sort_queries`: 1 = order queries along
  * the Morton curve before the search (default), 0 = caller's order, e.g. already coherent.
- * `method`: 0 = auto, 1 = thread-per-query traversal, 2 = warp-per-query traversal,
- * 3 = brute-force tiles, 4 = warp-shared walk, 5 = shared walk + per-lane scan queues,
- * 6 = lock-step Morton-window sweeps, 7 = lock-step nearest-first walks (auto for k <= 16),
- * 8 = sweep with nearest-first rescue, 9 = nearest-first walks with a shared-memory heap
- * (auto for 16 < k <= 32), 10 = method 7 on a persistent grid with lane refill (kept for study:
- * measured slower).  A method that cannot serve the requested k falls back to 2.
+ * `method`: 0 = auto, 2 = warp-per-query traversal (any k), 3 = brute-force tiles (k <= 16),
+ * 7 = lock-step nearest-first walks (auto for k <= 16), 9 = nearest-first walks with a shared-memory
+ * heap (auto for 16 < k <= 32).  A method that cannot serve the requested k falls back to 2.
+ * Methods 1, 4, 5, 6, 8, 10 and radius kernels 2, 3 are measured-slower variants that exist only in
+ * the study build (`make -C .../csrc STUDY=1` -> libpcnn_study.so, -DPCNN_STUDY); this library
+ * answers PCNN_ERR_UNSUPPORTED for them.
  * `sort_bits` (3..30, multiple of 3): leading Morton bits the query batch is ordered by.
- * `radius_batch`: radius kernel, 1 = auto (default), 0 = warp per query, 2 = runs of queries,
- * 3 = query per lane, 4 = warp per query with a dense stack walk, 5 = dense stack walk per run
- * of queries; `radius_run_div` (0 = auto), `radius_run_mult_count` / `radius_run_mult_fill`
+ * `radius_batch`: radius kernel, 1 = auto (default), 0 = warp per query, depth first (also the
+ * fallback for clouds of 2^30 points and more), 4 = warp per query with a dense stack walk (auto
+ * for sparse batches), 5 = dense stack walk per run of queries (auto for batches as dense as the
+ * cloud); `radius_run_div` (0 = auto), `radius_run_mult_count` / `radius_run_mult_fill`
  * (percent of the cloud's mean 8-point-group extent) size the runs.  Every choice returns the
  * same sets.
+ * `icp_certificates` (default 1): 0 makes the ICP loop search every source point in every
+ * iteration; the result is the same bit for bit (tests/test_gpu_configs.py), only slower.
  * Returns PCNN_ERR_INVALID for unknown names or values. */
 int pcnn_set_option(pcnn_index* index, const char* name, int value);
 /* With option "profile" = 1 every pcnn_knn / pcnn_radius_* call on this handle brackets its

@@ -85,3 +85,16 @@ def rot_err(Ta, Tb):
 
 def trans_err(Ta, Tb):
     return float(np.abs(np.asarray(Ta)[:3, 3] - np.asarray(Tb)[:3, 3]).max())
+
+
+def try_option(ix, name, value):
+    """set_option that reports False for kernel variants the shipped library does not hold (they
+    exist only in the -DPCNN_STUDY build, `make -C .../csrc STUDY=1`, run with PCNN_LIB=...)."""
+    import pcnn_b200 as pc
+    try:
+        ix.set_option(name, value)
+        return True
+    except pc.PcnnError as exc:
+        if exc.code == pc.api.ERR_UNSUPPORTED:
+            return False
+        raise

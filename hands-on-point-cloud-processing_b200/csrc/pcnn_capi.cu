@@ -160,6 +160,7 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
         int32_t* di = (int32_t*)hp->idx[b].p;
         float* dd = out_dist_host ? (float*)hp->d32[b].p : nullptr;
         double* dd64 = out_dist64_host ? (double*)hp->d64[b].p : nullptr;
+        NvtxRange nvtx_(index, "pcnn.knn_host.stage");
         e = cudaMemcpyAsync(dq, q_host + q0 * stride, sizeof(float) * (size_t)m * stride, cudaMemcpyHostToDevice, s);
         if (e != cudaSuccess) { set_error("pcnn_knn_host: H2D failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; break; }
         mark(s);

@@ -825,8 +825,12 @@ static int icp_launch_accumulate(pcnn_icp_state* st, int kind, cudaStream_t s) {
         for (int p = 0; p < st->world; p++) pv.box[p] = st->peer[p];
         pv.rank = st->rank; pv.world = st->world;
     }
-    icp_search_kernel<<<st->nblocks, ICP_THREADS, 0, s>>>(ix->view, st->cur, st->prev, st->prev2, st->cert, n, st->use_cert, st->gapk,
-                                                          st->move_frac, st->prm.max_corres_dist, st->dev);
+    {
+        NvtxRange nvtx_(ix, "pcnn.icp.search");
+        icp_search_kernel<<<st->nblocks, ICP_THREADS, 0, s>>>(ix->view, st->cur, st->prev, st->prev2, st->cert, n, st->use_cert, st->gapk,
+                                                              st->move_frac, st->prm.max_corres_dist, st->dev);
+    }
+    NvtxRange nvtx_(ix, kind == 2 ? "pcnn.icp.sums+exchange+solve" : (kind == 1 ? "pcnn.icp.sums+solve" : "pcnn.icp.sums"));
 #define PCNN_ICP_LAUNCH(MODE, KIND)                                                              \
     icp_accumulate_kernel<MODE, KIND><<<st->acc_blocks, ICP_THREADS, 0, s>>>(                       \
         ix->view, st->cur, st->nrm, st->prev, n, st->prm.max_corres_dist, st->prm.loss_epsilon, st->dev, st->partials, pv)

@@ -444,6 +444,9 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
             PCNN_CUDA(cudaEventCreate(&index->prof1));
         }
         index->opt_profile = value;
+    } else if (!std::strcmp(name, "nvtx")) {
+        PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: nvtx must be 0 or 1");
+        index->opt_nvtx = value;
     } else if (!std::strcmp(name, "icp_certificates")) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: icp_certificates must be 0 or 1");
         index->opt_icp_cert = value;

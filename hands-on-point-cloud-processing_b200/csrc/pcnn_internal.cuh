@@ -7,6 +7,7 @@
 #include <new>
 #include "../../include/pcnn.h"
 #include "pcnn_common.cuh"
+#include <nvtx3/nvToolsExt.h>
 
 struct pcnn_index {
     int kind = 0;
@@ -39,6 +40,7 @@ struct pcnn_index {
     int opt_coherent_budget2 = 600;  // ... and after the re-seed before it hands its queries over; 0 = never
     unsigned long long* dbg_warp_times = nullptr;  // diagnostics (pcnn_debug_warp_times)
     int opt_profile = 0;
+    int opt_nvtx = 0;           // 1: host-side NVTX ranges around the phases of every call on this handle (pcnn.knn.order, ...)
     int opt_icp_cert = 1;       // ICP correspondence certificates (pcnn_icp.cu); 0 = search every point every iteration
     cudaEvent_t prof0 = nullptr, prof1 = nullptr;  // bracket the last main search kernel
     // staging state of the host-pointer entry points (streams + device buffers), created on
@@ -148,6 +150,20 @@ void free_host_pipe(HostPipe* hp);
 inline cudaError_t wait_build(const pcnn_index* ix, cudaStream_t s) {
     return ix->ev_end ? cudaStreamWaitEvent(s, ix->ev_end, 0) : cudaSuccess;
 }
+
+// NVTX range over the host-side enqueue of one phase (a profiler correlates the kernels launched inside
+// it); one predictable branch when the option is off.
+struct NvtxRange {
+    bool on;
+    NvtxRange(const pcnn_index* ix, const char* name) : on(ix && ix->opt_nvtx) {
+        if (on) nvtxRangePushA(name);
+    }
+    ~NvtxRange() {
+        if (on) nvtxRangePop();
+    }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 // profile brackets: no-ops unless option "profile" is set
 inline void prof_begin(const pcnn_index* ix, cudaStream_t s) {

@@ -34,6 +34,7 @@ __global__ void query_code_kernel(const float* __restrict__ q, int nq, int strid
 
 int sort_queries(const pcnn_index* ix, const float* q, int64_t nq, int stride, unsigned** perm_out,
                  Scratch& sc, cudaStream_t s) {
+    NvtxRange nvtx_(ix, "pcnn.query_order");
     const int n = (int)nq;
     unsigned *c0, *c1, *p0, *p1, *hist;
     PCNN_CUDA(sc.get(&c0, (size_t)n));
@@ -64,6 +65,7 @@ __global__ void query_code64_kernel(const float* __restrict__ q, int nq, int str
 
 int sort_queries_fine(const pcnn_index* ix, const float* q, int64_t nq, int stride, int bits, unsigned** perm_out,
                       Scratch& sc, cudaStream_t s) {
+    NvtxRange nvtx_(ix, "pcnn.query_order");
     const int n = (int)nq;
     unsigned long long *c0, *c1;
     unsigned *p0, *p1, *hist;
@@ -1539,6 +1541,7 @@ static void launch_brute_k(const pcnn_index* ix, const float* q, int nq, int str
 int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, int k, int32_t* out_idx,
                float* out_dist, double* out_dist64, cudaStream_t s) {
     if (nq64 == 0) return PCNN_OK;
+    NvtxRange nvtx_(ix, "pcnn.knn");
     const int nq = (int)nq64;
     int method = ix->opt_method;
 #ifndef PCNN_STUDY

@@ -642,6 +642,7 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
         PCNN_CUDA(cudaMemsetAsync(out_offsets, 0, sizeof(int64_t), s));
         return PCNN_OK;
     }
+    NvtxRange nvtx_(ix, "pcnn.radius.count");
     const WarpPlan wp = make_warp_plan(ix->view, ix->opt_radius_leaf_level);
     const RadiusThr rt = make_thr(radius);
     Scratch sc(s);
@@ -680,6 +681,7 @@ int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq64, int 
             ix->view, wp, q, nq, stride, perm, rt, counts, nullptr, nullptr, nullptr, nullptr);
     }
     prof_end(ix, s);
+    NvtxRange nvtx_scan(ix, "pcnn.radius.scan");
     if (int rc = scan_counts(counts, nq, (long long*)out_offsets, sc, s)) return rc;
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
@@ -690,6 +692,7 @@ int launch_radius_fill(const pcnn_index* ix, const float* q, int64_t nq64, int s
                        cudaStream_t s) {
     const int nq = (int)nq64;
     if (nq == 0) return PCNN_OK;
+    NvtxRange nvtx_(ix, "pcnn.radius.fill");
     const WarpPlan wp = make_warp_plan(ix->view, ix->opt_radius_leaf_level);
     const RadiusThr rt = make_thr(radius);
     Scratch sc(s);

@@ -142,6 +142,9 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
  * same sets.
  * `icp_certificates` (default 1): 0 makes the ICP loop search every source point in every
  * iteration; the result is the same bit for bit (tests/test_gpu_configs.py), only slower.
+ * `nvtx` (default 0): 1 wraps the host-side enqueue of every phase of the calls on this handle in
+ * NVTX ranges (pcnn.query_order, pcnn.knn, pcnn.knn_host.stage, pcnn.radius.count / .scan / .fill,
+ * pcnn.icp.search, pcnn.icp.sums[+exchange][+solve]) for a profiler timeline.
  * Returns PCNN_ERR_INVALID for unknown names or values. */
 int pcnn_set_option(pcnn_index* index, const char* name, int value);
 /* With option "profile" = 1 every pcnn_knn / pcnn_radius_* call on this handle brackets its

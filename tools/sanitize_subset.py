@@ -17,6 +17,7 @@ src, tar, nrm, T = pc.synth.icp_pair(N, seed=pc.synth.BASE_SEED + 3)
 dev = torch.device("cuda", 0)
 ix = pc.Index(torch.from_numpy(tar).to(dev))
 dq = torch.from_numpy(src).to(dev)
+ix.set_option("nvtx", 1)  # the ranges are exercised too
 for k in (8, 32, 64):
     ix.knn(dq, k, dist="f64")
 ix.set_option("method", 3); ix.knn(dq[:512], 8); ix.set_option("method", 0)

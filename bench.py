@@ -635,7 +635,7 @@ def run_gpu(args):
     e2e = {"value": world * N_QUERIES * args.steps / e2e_s, "unit": "queries/s",
            "h2d_bytes_per_step": int(h_q.nbytes), "d2h_bytes_per_step": int(h_idx.nbytes + h_dist.nbytes),
            "ms_per_step": 1e3 * e2e_s / args.steps,
-           "api": "pcnn_knn_host (C ABI), pinned host buffers, 8 stages on 8 streams",
+           "api": "pcnn_knn_host (C ABI), pinned host buffers, 10 stages on 8 streams, one search launch per stage",
            "copy_ceiling": {"queries_per_s": world * N_QUERIES * args.steps / copy_s, "ms_per_step": 1e3 * copy_s / args.steps,
                             "aggregate_GBps": world * args.steps * (h_q.nbytes + h_idx.nbytes + h_dist.nbytes) / copy_s / 1e9,
                             "what": "the step's H2D + D2H alone from the same pinned buffers, all ranks at once, no kernels"},

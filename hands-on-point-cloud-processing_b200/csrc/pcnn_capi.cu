@@ -1,7 +1,7 @@
 // pcnn_capi.cu -- C ABI entry points for kNN / radius search (declared in include/pcnn.h).
 // Device-pointer variants validate and enqueue; host-pointer variants stage through HBM in
 // stages on up to eight streams so that the PCIe copies of one chunk overlap the kernels of the
-// next (the reference has no device boundary: Homework2/hw2/include/benchmark.hpp:59-72).
+// next, each stage searched in the caller's order (one launch per stage) (the reference has no device boundary: Homework2/hw2/include/benchmark.hpp:59-72).
 #include <algorithm>
 #include <cstdlib>
 #include <vector>
@@ -36,12 +36,9 @@ void free_host_pipe(HostPipe* hp) {
 
 namespace {
 
-// pipeline stage size: enough stages to hide the PCIe copies behind the kernels, few enough
-// that the ~14 launches per stage (70 us of host time) stay ahead of the device.  Measured
-// with PCNN_PIPE_TRACE on 1M queries, k = 8: 4 stages on 3 streams 1.88 ms, 8 stages on 8
-// streams 1.75 ms (the result copy then runs back to back from the end of the first stage, at
-// 50 GB/s, and the searches keep just ahead of it); shorter first stages gain nothing because
-// the query ordering of a stage is launch-latency bound (~0.2 ms whatever its size).
+// pipeline stage size: enough stages to hide the PCIe copies behind the kernels.  Measured on 1M queries,
+// k = 8 (tools/e2e_sweep.sh, B200): stages of 65k / 125k / 131k / 200k queries -> 1.55 / 1.55 / 1.56 /
+// 1.58 ms per call; round 1's pipeline, which ordered every stage's queries, took 1.82 ms.
 int64_t host_chunk(int64_t nq) {
 #ifdef PCNN_STUDY
     if (const char* e = std::getenv("PCNN_HOST_CHUNK")) {  // tuning aid
@@ -114,12 +111,31 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
     HostPipe* hp = nullptr;
     rc = get_pipe(ix, &hp, "pcnn_knn_host");
     if (rc != PCNN_OK) return rc;
+    // Stage plan.  The link is the bottleneck of this call (64 MB of results at ~55 GB/s = 1.16 ms for 1M
+    // queries, k = 8, against 1.05 ms of search), so what matters is how soon the first result byte
+    // leaves and that the copy engine never starves afterwards.  Stages are searched in the CALLER'S
+    // order: ordering a stage's queries along the curve is a chain of 13 small dependent kernels that
+    // crawls (0.2-0.6 ms) while another stage's search fills the GPU, and it buys only 0.17-0.23 ms of
+    // search time per million queries (1.05 ms ordered, 1.21 ms on LiDAR scan order, 1.27 ms on a random
+    // shuffle; tools/knn_unsorted.py).  Rows do not depend on the order.  Two small stages lead so that
+    // results are on the wire after ~0.2 ms.
+    struct Stage { int64_t q0, m; int sort; };
+    std::vector<Stage> plan;
     const int64_t chunk = host_chunk(nq);
+    {
+        int64_t q0 = 0;
+        if (nq >= 4 * chunk) {
+            plan.push_back({0, 32768, 0});
+            plan.push_back({32768, 65536, 0});
+            q0 = 32768 + 65536;
+        }
+        for (; q0 < nq; q0 += chunk) plan.push_back({q0, std::min<int64_t>(chunk, nq - q0), 0});
+    }
     int max_streams = HOST_STREAMS;
 #ifdef PCNN_STUDY
     if (const char* ev = std::getenv("PCNN_HOST_STREAMS")) max_streams = std::max(1, std::min(HOST_STREAMS, std::atoi(ev)));  // tuning aid
 #endif
-    const int nstreams = (int)std::min<int64_t>(max_streams, (nq + chunk - 1) / chunk);
+    const int nstreams = (int)std::min<size_t>((size_t)max_streams, plan.size());
     cudaError_t e = cudaSuccess;
     for (int i = 0; i < nstreams && e == cudaSuccess; i++) {
         e = hp->q[i].ensure(sizeof(float) * (size_t)chunk * stride);
@@ -131,7 +147,7 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
         set_error("pcnn_knn_host: staging allocation failed: %s", cudaGetErrorString(e));
         return PCNN_ERR_NOMEM;
     }
-    // PCNN_PIPE_TRACE=1 (tuning aid): per-stage event times of this call on stderr
+    // PCNN_PIPE_TRACE=1 (tuning aid, study build): per-stage event times of this call on stderr
 #ifdef PCNN_STUDY
     static const bool trace = std::getenv("PCNN_PIPE_TRACE") != nullptr;
 #else
@@ -150,11 +166,9 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
     };
     for (int i = 0; i < nstreams; i++) wait_build(index, hp->s[i]);  // a device-side build may still be running on its own stream
     mark(hp->s[0]);
-    int c = 0;
-    int64_t m = 0;
-    for (int64_t q0 = 0; q0 < nq && rc == PCNN_OK; q0 += m, c++) {
-        const int b = c % nstreams;
-        m = std::min<int64_t>(chunk, nq - q0);
+    for (size_t c = 0; c < plan.size() && rc == PCNN_OK; c++) {
+        const int b = (int)(c % (size_t)nstreams);
+        const int64_t q0 = plan[c].q0, m = plan[c].m;
         cudaStream_t s = hp->s[b];
         float* dq = (float*)hp->q[b].p;
         int32_t* di = (int32_t*)hp->idx[b].p;
@@ -164,7 +178,7 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
         e = cudaMemcpyAsync(dq, q_host + q0 * stride, sizeof(float) * (size_t)m * stride, cudaMemcpyHostToDevice, s);
         if (e != cudaSuccess) { set_error("pcnn_knn_host: H2D failed: %s", cudaGetErrorString(e)); rc = PCNN_ERR_CUDA; break; }
         mark(s);
-        rc = launch_knn(index, dq, m, stride, k, di, dd, dd64, s);
+        rc = launch_knn(index, dq, m, stride, k, di, dd, dd64, s, plan[c].sort);
         if (rc != PCNN_OK) break;
         mark(s);
         e = cudaMemcpyAsync(out_idx_host + q0 * k, di, sizeof(int32_t) * (size_t)m * k, cudaMemcpyDeviceToHost, s);

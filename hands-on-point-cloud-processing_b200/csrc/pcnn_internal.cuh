@@ -174,8 +174,10 @@ inline void prof_end(const pcnn_index* ix, cudaStream_t s) {
 }
 
 // kernels / launchers implemented across the .cu files
+// sort_override: -1 = the handle's sort_queries option, 0 / 1 = this call only (the first, small stages
+// of the host pipeline go unsorted so that result bytes start to flow early)
 int launch_knn(const pcnn_index* ix, const float* q, int64_t nq, int stride, int k, int32_t* out_idx,
-               float* out_dist, double* out_dist64, cudaStream_t s);
+               float* out_dist, double* out_dist64, cudaStream_t s, int sort_override = -1);
 int launch_radius_count(const pcnn_index* ix, const float* q, int64_t nq, int stride, double radius,
                         int64_t* out_offsets, cudaStream_t s);
 // exclusive scan of nq int64 counts into offsets[nq + 1] (pcnn_radius.cu)

@@ -1539,8 +1539,9 @@ static void launch_brute_k(const pcnn_index* ix, const float* q, int nq, int str
 }
 
 int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, int k, int32_t* out_idx,
-               float* out_dist, double* out_dist64, cudaStream_t s) {
+               float* out_dist, double* out_dist64, cudaStream_t s, int sort_override) {
     if (nq64 == 0) return PCNN_OK;
+    const int sortq = sort_override >= 0 ? sort_override : ix->opt_sort_queries;
     NvtxRange nvtx_(ix, "pcnn.knn");
     const int nq = (int)nq64;
     int method = ix->opt_method;
@@ -1556,7 +1557,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     if (method == 9) {
         Scratch sc(s);
         unsigned* perm = nullptr;
-        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+        if (sortq && nq > 32 && ix->n > 0) {
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }
@@ -1568,7 +1569,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     } else if (method == 8) {
         Scratch sc(s);
         unsigned* perm = nullptr;
-        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+        if (sortq && nq > 32 && ix->n > 0) {
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }
@@ -1582,7 +1583,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     } else if (method == 10) {
         Scratch sc(s);
         unsigned* perm = nullptr;
-        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+        if (sortq && nq > 32 && ix->n > 0) {
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }
@@ -1600,7 +1601,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     } else if (method == 7) {
         Scratch sc(s);
         unsigned* perm = nullptr;
-        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+        if (sortq && nq > 32 && ix->n > 0) {
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }
@@ -1616,7 +1617,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     } else if (method == 6) {
         Scratch sc(s);
         unsigned* perm = nullptr;
-        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+        if (sortq && nq > 32 && ix->n > 0) {
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }
@@ -1630,7 +1631,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     } else if (method == 5) {
         Scratch sc(s);
         unsigned* perm = nullptr;
-        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+        if (sortq && nq > 32 && ix->n > 0) {
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }
@@ -1644,7 +1645,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     } else if (method == 4) {
         Scratch sc(s);
         unsigned* perm = nullptr;
-        if (ix->opt_sort_queries && nq > 32 && ix->n > 0) {
+        if (sortq && nq > 32 && ix->n > 0) {
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }
@@ -1672,7 +1673,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
     } else if (method == 1) {
         Scratch sc(s);
         unsigned* perm = nullptr;
-        if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {
+        if (sortq && nq > 1024 && ix->n > 0) {
             int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
             if (rc != PCNN_OK) return rc;
         }

@@ -127,6 +127,8 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
 
 /* Query-side knobs (all have working defaults).  `sort_queries`: 1 = order queries along
  * the Morton curve before the search (default), 0 = caller's order, e.g. already coherent.
+ * (pcnn_knn_host always searches its pipeline stages in the caller's order: there the ordering costs
+ * more latency than it saves search time; rows never depend on the order.)
  * `method`: 0 = auto, 2 = warp-per-query traversal (any k), 3 = brute-force tiles (k <= 16),
  * 7 = lock-step nearest-first walks (auto for k <= 16), 9 = nearest-first walks with a shared-memory
  * heap (auto for 16 < k <= 32).  A method that cannot serve the requested k falls back to 2.

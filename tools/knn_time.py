@@ -1,0 +1,21 @@
+"""Developer tool (GPU box): kernel time of the shipped batched kNN on the bench clouds (1M x 1M),
+K from the environment (default 8), best of 5; prints a checksum of the rows so that two builds can be
+compared bit for bit.  Small enough to run under ncu (-k regex:knn_dfs)."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np, torch
+import pcnn_b200 as pc
+import bench
+pts, nrm, qry = bench.make_clouds(0)
+dev = torch.device("cuda", 0)
+ix = pc.Index(torch.from_numpy(pts).to(dev))
+ix.set_option("profile", 1)
+dq = torch.from_numpy(qry).to(dev)
+for K in [int(x) for x in os.environ.get("KS", "8").split(",")]:
+    best = 1e9
+    for _ in range(int(os.environ.get("REPS", "5"))):
+        idx, dist = ix.knn(dq, K, dist="f64")
+        best = min(best, ix.last_kernel_ms())
+    chk = int((idx.to(torch.int64) * torch.arange(1, K + 1, device=dev)).sum().item()) ^ int(dist.view(torch.int64).sum().item())
+    print("k=%d kernel %.4f ms  %.1f M q/s  checksum %x" % (K, best, len(qry) / best / 1e3, chk & 0xffffffffffff), flush=True)

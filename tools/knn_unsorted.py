@@ -25,3 +25,18 @@ for name, qq in sets.items():
             e1.record(); torch.cuda.synchronize()
             best = min(best, (e0.elapsed_time(e1), ix.last_kernel_ms()))
         print("%-10s sort_queries=%d: call %.3f ms, search kernel %.3f ms" % (name, sort, best[0], best[1]), flush=True)
+ix.set_option("sort_queries", 1)
+dq = torch.from_numpy(np.ascontiguousarray(sets["shuffled"])).to(dev)
+dq2 = torch.from_numpy(np.ascontiguousarray(sets["scan order"])).to(dev)
+for bits in (30, 27, 24, 21, 18, 15):
+    ix.set_option("sort_bits", bits)
+    row = []
+    for d in (dq2, dq):
+        best = (1e9, 1e9)
+        for _ in range(5):
+            torch.cuda.synchronize(); e0.record()
+            ix.knn(d, 8, dist="f32")
+            e1.record(); torch.cuda.synchronize()
+            best = min(best, (e0.elapsed_time(e1), ix.last_kernel_ms()))
+        row.append("call %.3f ms (kernel %.3f)" % best)
+    print("sort_bits=%d: scan order %s | shuffled %s" % (bits, row[0], row[1]), flush=True)

@@ -305,6 +305,7 @@ __device__ double peer_exchange(const PeerView& pv, Dev* st, int col, double r) 
 #define PCNN_ICP_MINBLOCKS 8
 #endif
 constexpr int ICP_J = 4;  // slices of 128 source points a block takes together
+constexpr int ICP_COOP_MAX = 4;  // a warp left with this many points to search takes them one at a time, all lanes on one (nn1_coop)
 
 // Correspondence certificate.  A search at position c found the nearest target point x1 and a
 // floor key2 under the keys of all others (Best2f).  With u = 2^-24 the float32 key of nanoflann is
@@ -335,8 +336,10 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, int* prev2, float4* cert
     __shared__ float s_ql[LS_QDEPTH][ICP_THREADS];
     __shared__ unsigned short s_list[ICP_J * ICP_THREADS];  // (slice of the group, thread) of a point to search
     __shared__ float s_move[ICP_J * ICP_THREADS];           // how far T_delta moved the point
-    __shared__ int s_nwalk;
+    __shared__ unsigned s_co_stack[ICP_THREADS / 32][CO_STACK];  // nn1_coop: one query, the whole warp
+    __shared__ unsigned s_co_gl[ICP_THREADS / 32][CO_GLIST];
     if (st->done) return;  // uniform: loop already ended (converged / failed)
+    int walked_here = 0;
     const float move_max = move_frac * __ldg(iv.cube + 8);
     const float gap_min = 1e-3f * __ldg(iv.cube + 8) + 1e-6f;  // rides out the last-bit jitter of a converged pose
     const bool first_done = st->iters > 0 || st->unchanged > 0 || st->last_pairs > 0;
@@ -358,8 +361,8 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, int* prev2, float4* cert
     // so a nearly converged iteration runs a few dense warps instead of every warp for its one or
     // two uncertified lanes.  The sums are not live here: the walk gets the registers.
     for (int s0 = blockIdx.x; s0 < nsl; s0 += J * G) {
-        if (threadIdx.x == 0) s_nwalk = 0;
-        __syncthreads();
+        int nw = 0;  // points of THIS WARP's lanes (J slices x 32) that need a search
+        unsigned short* const wlist = s_list + warp * (J * 32);
         int tj[J], ppj[J], pp2j[J];
         float4 pj[J], cj[J];
 #pragma unroll
@@ -412,18 +415,53 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, int* prev2, float4* cert
                 need = !cert_holds(pj[j], cj[j], k1);
             }
             const unsigned m = __ballot_sync(full, need);
-            int at = 0;
-            if (lane == 0 && m) at = atomicAdd(&s_nwalk, __popc(m));
-            at = __shfl_sync(full, at, 0);
-            if (need) s_list[at + __popc(m & ((1u << lane) - 1u))] = (unsigned short)(j * ICP_THREADS + threadIdx.x);
+            if (need) wlist[nw + __popc(m & ((1u << lane) - 1u))] = (unsigned short)(j * ICP_THREADS + threadIdx.x);
+            nw += __popc(m);
         }
-        __syncthreads();
-        const int nw = s_nwalk;
-        if (threadIdx.x == 0 && nw) atomicAdd(&st->walked, (unsigned long long)nw);
-        for (int b = warp << 5; b < nw; b += ICP_THREADS) {  // whole warps; tail lanes shadow the last entry
+        // The list is per WARP: nothing below waits for another warp of the block (the block-wide list of
+        // round 1 cost two block barriers per 512 points, every warp waiting for the block's longest walk;
+        // its purpose, packing sparse needs into dense warps, is served by nn1_coop now).
+        __syncwarp();
+        walked_here += nw;
+        for (int b = 0; b < nw; b += 32) {  // tail lanes shadow the last entry
+            if (nw - b <= ICP_COOP_MAX) {
+                // a handful of points (the usual case once the pose has settled: one or two uncertified
+                // points per block): one at a time with the whole warp on it, instead of one lane walking
+                // for 30-60 us with 31 shadows.  Same correspondence, same kind of certificate.
+                for (int r = b; r < nw; r++) {
+                    const int e = wlist[r];
+                    const int t = (s0 + (e / ICP_THREADS) * G) * ICP_THREADS + (e % ICP_THREADS);
+                    const float4 p = cur[t];
+                    const int pp = prev[t];
+                    const float moved = s_move[e];
+                    const float gap = (use_cert && first_done && moved < move_max) ? gapk * moved + gap_min : -1.f;
+                    const int seed = pp >= 0 ? (pp >> PCNN_GROUP_LOG) : -1;
+                    if (gap < 0.f) {
+                        Best1f best;
+                        nn1_coop(iv, p.x, p.y, p.z, seed, max_corres_dist, best, s_co_stack[warp], s_co_gl[warp]);
+                        if (lane == 0) {
+                            prev[t] = best.pos;
+                            prev2[t] = -1;
+                            cert[t] = make_float4(p.x, p.y, p.z, -1.f);
+                        }
+                    } else {
+                        Best2f best;
+                        best.gap = gap;
+                        const float rr = __fadd_ru(__fmul_ru(__fsqrt_ru(max_corres_dist), 1.0001f), gap);  // as Best2f::reach
+                        nn1_coop(iv, p.x, p.y, p.z, seed, __fmul_ru(rr, rr), best, s_co_stack[warp], s_co_gl[warp]);
+                        if (lane == 0) {
+                            prev[t] = best.pos;
+                            prev2[t] = (best.pos2 >= 0 && best.key2 < best.floor_key()) ? best.pos2 : -1;
+                            cert[t] = make_float4(p.x, p.y, p.z, cert_radius(best.floor_key()));
+                        }
+                    }
+                    __syncwarp();
+                }
+                continue;
+            }
             const int i = b + lane;
             const bool live = i < nw;
-            const int e = s_list[live ? i : nw - 1];
+            const int e = wlist[live ? i : nw - 1];
             const int t = (s0 + (e / ICP_THREADS) * G) * ICP_THREADS + (e % ICP_THREADS);
             const float4 p = cur[t];
             const int pp = prev[t];
@@ -461,8 +499,9 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, int* prev2, float4* cert
                 }
             }
         }
-        __syncthreads();  // s_list is reused
+        __syncwarp();  // the warp's list is reused
     }
+    if (lane == 0 && walked_here) atomicAdd(&st->walked, (unsigned long long)walked_here);
 }
 
 // Kernel 2 of an iteration: the pairs' terms, their reduction, and (KIND) the solve / the exchange.

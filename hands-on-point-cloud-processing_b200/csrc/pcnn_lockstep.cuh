@@ -132,4 +132,133 @@ __device__ __forceinline__ void nn1_lockstep(const IndexView& iv, float qx, floa
     }
 }
 
+// ------------------------------------------------------------------ one query, the whole warp
+// nn1_coop: the same exact float32 1-NN for ONE query with all 32 lanes working on it.  The lock-step
+// walk above runs at the pace of its longest walk; a warp that holds a single real query (what a
+// nearly converged ICP iteration is made of: a few uncertified points, one per block) then spends
+// 30-60 us walking alone, with the kernel waiting for it (ncu, converged 1M-point iteration: the SMs
+// are active 21 us of the kernel's 49).  Here the warp keeps a stack of nodes in shared memory, pops
+// up to 16 and tests their 32 children at once (as radius_stack_kernel), and scans 16 queued groups
+// (128 points, four independent loads per lane) per step.  Every lane keeps a PARTIAL result over the
+// points it happened to test and prunes with the warp-wide minimum of the partial pruning keys, which
+// is never below the pruning key of the merged result (min of reach(key) is reach of the min; a lane's
+// third-smallest key is at least the third-smallest of the union): nothing is pruned that the merged
+// search would have kept, and every pruned box exceeds the final floor.  Partial results are merged
+// by a butterfly at the end; all lanes return the merged result.
+constexpr int CO_STACK = 256;  // stack entries per warp (growth bound: see radius_stack_kernel)
+constexpr int CO_GLIST = 64;   // queued groups per warp
+constexpr unsigned CO_NODE_MASK = 0x07ffffffu;
+
+__device__ __forceinline__ float warp_min_nonneg(float v) {  // v >= 0 (or +inf): float order = bit order
+    return __uint_as_float(__reduce_min_sync(0xffffffffu, __float_as_uint(v)));
+}
+
+__device__ __forceinline__ void best_merge_xor(Best1f& a, int o) {
+    const unsigned full = 0xffffffffu;
+    const float k = __shfl_xor_sync(full, a.key, o);
+    const int i = __shfl_xor_sync(full, a.idx, o), p = __shfl_xor_sync(full, a.pos, o);
+    if (kless32(k, i, a.key, a.idx)) { a.key = k; a.idx = i; a.pos = p; }
+}
+// Two partial Best2f over DISJOINT point sets: the better best wins; the runner-up is the smallest
+// key among the loser's best and the two old runners-up (the loser's runner-up cannot beat the loser's
+// best); whatever is left joins `lim`.  Entries that stand for "nothing found" carry the start bound
+// and position -1, exactly as after start().
+__device__ __forceinline__ void best_merge_xor(Best2f& a, int o) {
+    const unsigned full = 0xffffffffu;
+    const float bk = __shfl_xor_sync(full, a.key, o), bk2 = __shfl_xor_sync(full, a.key2, o), bl = __shfl_xor_sync(full, a.lim, o);
+    const int bi = __shfl_xor_sync(full, a.idx, o), bp = __shfl_xor_sync(full, a.pos, o), bp2 = __shfl_xor_sync(full, a.pos2, o);
+    const bool bw = kless32(bk, bi, a.key, a.idx);
+    const float wk = bw ? bk : a.key, lk = bw ? a.key : bk;            // winner's / loser's best
+    const int wi = bw ? bi : a.idx, wp = bw ? bp : a.pos, lp = bw ? a.pos : bp;
+    const float wk2 = bw ? bk2 : a.key2, lk2 = bw ? a.key2 : bk2;      // their runners-up
+    const int wp2 = bw ? bp2 : a.pos2;
+    float rest;
+    if (wk2 < lk) { a.key2 = wk2; a.pos2 = wp2; rest = lk; }
+    else { a.key2 = lk; a.pos2 = lp; rest = fminf(wk2, lk2); }
+    a.key = wk; a.idx = wi; a.pos = wp;
+    a.lim = fminf(fminf(a.lim, bl), rest);
+    a.prune = fminf(a.lim, a.reach(wk));
+}
+
+// s_stack [CO_STACK], s_gl [CO_GLIST]: this warp's shared memory.  qx, qy, qz, seed_group and bound are
+// warp-uniform; `best` comes in with its parameters set (Best2f::gap) and returns the merged result in
+// every lane.  Every lane of the warp must call this together.
+template <class BEST>
+__device__ __forceinline__ void nn1_coop(const IndexView& iv, float qx, float qy, float qz, int seed_group,
+                                         float bound, BEST& best, unsigned* s_stack, unsigned* s_gl) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    best.start(bound);
+    if (iv.n <= 0) return;
+    if (seed_group < 0 || seed_group >= iv.n0) seed_group = home_group(iv, morton63(qx, qy, qz, iv.cube, iv.cube[3]));
+    {
+        const int pos = (seed_group << PCNN_GROUP_LOG) + (lane & 7);
+        if (lane < PCNN_GROUP && pos < iv.n) {
+            const float4 p = __ldg(iv.pts + pos);
+            best.offer(key32(p.x, p.y, p.z, qx, qy, qz), __float_as_int(p.w), pos);
+        }
+    }
+    float wb = warp_min_nonneg(best.bound());
+    const int top = iv.nlev - 1;
+    int sp = 0, gc = 0;
+    if (top > 0) {
+        const int l = walk_start_level(iv, seed_group, qx, qy, qz, wb);
+        if (lane == 0) s_stack[0] = (unsigned)(seed_group >> l) | ((unsigned)l << 27);
+        sp = 1;
+    }
+    __syncwarp();
+    while (sp > 0 || gc > 0) {
+        if (gc >= 16 || sp == 0) {
+            // scan up to 16 queued groups (taken from the end of the list): four points per lane
+            const int take = gc < 16 ? gc : 16, base = gc - take;
+            float4 p[4];
+            int ps[4];
+            bool v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int it = base + 4 * u + (lane >> 3);
+                v[u] = it < gc;
+                ps[u] = v[u] ? ((int)s_gl[it] << PCNN_GROUP_LOG) + (lane & 7) : 0;
+                v[u] = v[u] && ps[u] < iv.n;
+                if (v[u]) p[u] = __ldg(iv.pts + ps[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                if (v[u]) best.offer(key32(p[u].x, p[u].y, p[u].z, qx, qy, qz), __float_as_int(p[u].w), ps[u]);
+            gc = base;
+            wb = warp_min_nonneg(best.bound());
+            __syncwarp();
+            continue;
+        }
+        const int k = sp <= CO_STACK - 80 ? (sp < 16 ? sp : 16) : 1;
+        const int sh = k > 8 ? 1 : (k > 4 ? 2 : (k > 2 ? 3 : (k > 1 ? 4 : (sp <= CO_STACK - 80 ? 5 : 1))));
+        const int en = lane >> sh, sub = lane & ((1 << sh) - 1);
+        const unsigned ent = en < k ? s_stack[sp - k + en] : 0u;
+        sp -= k;
+        const int lvl = (int)(ent >> 27);
+        const int she = sh < lvl ? sh : lvl;
+        const int L = lvl - she;
+        const int nd = ((int)(ent & CO_NODE_MASK) << she) + sub;
+        bool pass = false;
+        if (en < k && sub < (1 << she) && nd < (int)(((unsigned)iv.n0 + (1u << L) - 1u) >> L)) {
+            const float4* b = iv.box + 2 * ((size_t)iv.lev_off[L] + nd);
+            // strict test: a box at exactly the best key may hold a lower index
+            pass = !(boxlb32(__ldg(b), __ldg(b + 1), qx, qy, qz) > wb);
+        }
+        __syncwarp();  // every lane has read its entry before the pushes below reuse the slots
+        const bool to_stack = pass && L > 0;
+        const unsigned ms = __ballot_sync(full, to_stack);
+        if (to_stack) s_stack[sp + __popc(ms & lt)] = (unsigned)nd | ((unsigned)L << 27);
+        sp += __popc(ms);
+        const bool to_list = pass && L == 0 && nd != seed_group;
+        const unsigned mg = __ballot_sync(full, to_list);
+        if (to_list) s_gl[gc + __popc(mg & lt)] = (unsigned)nd;
+        gc += __popc(mg);
+        __syncwarp();
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best_merge_xor(best, o);
+}
+
 }  // namespace pcnn

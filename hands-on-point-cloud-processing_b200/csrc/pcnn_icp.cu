@@ -819,10 +819,37 @@ nn1_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride, const 
     }
 }
 
+// Small batches: one WARP per query (nn1_coop).  A few hundred queries cannot fill the device one per
+// lane, and each would walk alone at the pace of its dependent loads; with 32 lanes per query the
+// same batch finishes in a fraction of the time.  Same result, bit for bit.
+constexpr int NN1_COOP_MAX_QUERIES = 2048;
+__global__ void __launch_bounds__(128)
+nn1_coop_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride, int32_t* __restrict__ out_idx,
+                float* __restrict__ out_d2) {
+    __shared__ unsigned s_stack[4][CO_STACK];
+    __shared__ unsigned s_gl[4][CO_GLIST];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qi = blockIdx.x * 4 + warp;
+    if (qi >= nq) return;  // warp-uniform
+    const float* qp = q + (size_t)qi * stride;
+    Best1f best;
+    nn1_coop(iv, qp[0], qp[1], qp[2], -1, __int_as_float(0x7f800000), best, s_stack[warp], s_gl[warp]);
+    if (lane == 0) {
+        out_idx[qi] = best.pos >= 0 ? best.idx : -1;
+        if (out_d2) out_d2[qi] = best.key;
+    }
+}
+
 int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq64, int stride, int32_t* out_idx,
                float* out_d2, cudaStream_t s) {
     const int nq = (int)nq64;
     if (nq == 0) return PCNN_OK;
+    NvtxRange nvtx_(ix, "pcnn.nn1");
+    if (nq <= NN1_COOP_MAX_QUERIES) {
+        nn1_coop_kernel<<<(nq + 3) / 4, 128, 0, s>>>(ix->view, q, nq, stride, out_idx, out_d2);
+        PCNN_CUDA(cudaGetLastError());
+        return PCNN_OK;
+    }
     Scratch sc(s);
     unsigned* perm = nullptr;
     if (ix->opt_sort_queries && nq > 1024 && ix->n > 0) {

@@ -287,7 +287,9 @@ int pcnn_icp_peer_detach(pcnn_icp_state* st);
 
 /* Exact float32 1-NN of every query against the index, as the ICP loop uses it
  * (nanoflann.hpp:383-408 key: ((dx*dx)+dy*dy)+dz*dz in float32, dx = q - p; lowest index
- * wins an exact tie).  out_idx [nq], out_d2 [nq]. */
+ * wins an exact tie).  out_idx [nq], out_d2 [nq].  Batches of up to 2048 queries run one WARP per
+ * query (32 child boxes tested and 128 points scanned per step, per-lane partial results merged at
+ * the end); larger ones one query per lane in lock step.  Same result either way. */
 int pcnn_nn1_f32(const pcnn_index* index, const float* q_dev, int64_t nq, int stride,
                  int32_t* out_idx_dev, float* out_d2_dev, pcnn_stream stream);
 

@@ -144,6 +144,9 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
  * same sets.
  * `icp_certificates` (default 1): 0 makes the ICP loop search every source point in every
  * iteration; the result is the same bit for bit (tests/test_gpu_configs.py), only slower.
+ * `icp_pdl` (default 1): the two kernels of an ICP iteration are launched with programmatic
+ * stream serialization (the successor's launch overlaps the predecessor) when the source cloud does
+ * not fill the device; 0 = plain launches.  Same result either way.
  * `nvtx` (default 0): 1 wraps the host-side enqueue of every phase of the calls on this handle in
  * NVTX ranges (pcnn.query_order, pcnn.knn, pcnn.knn_host.stage, pcnn.radius.count / .scan / .fill,
  * pcnn.icp.search, pcnn.icp.sums[+exchange][+solve]) for a profiler timeline.

@@ -12,6 +12,11 @@ dev = torch.device("cuda", 0)
 
 
 def study(name, ix, d_src, d_nrm, mode, iters=30):
+    for pdl in (0, 1):
+        ix.set_option("icp_pdl", pdl)
+        ix.icp(d_src, tar_normals=d_nrm, max_iter=3, mode=mode)
+        best = min(ix.icp(d_src, tar_normals=d_nrm, max_iter=iters, mode=mode)["loop_ms"] for _ in range(3))
+        print("%s: icp_pdl=%d fused loop %.1f us/iter" % (name, pdl, 1e3 * best / iters), flush=True)
     ix.icp(d_src, tar_normals=d_nrm, max_iter=3, mode=mode)
     st = pc.IcpState(ix, d_src, tar_normals=d_nrm, max_iter=iters, mode=mode)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * iters + 1)]

@@ -41,6 +41,34 @@ struct IndexView {
     const float* cube;  // [8]: bbox min.xyz, 2^21 / cube side, bbox max.xyz, cube side
 };
 
+#if defined(__CUDACC__)
+// Programmatic dependent launch.  A kernel launched with launch_pdl(..., pdl = true) may have its blocks
+// become resident while its predecessor in the stream still runs; pdl_prologue(), the FIRST thing such a
+// kernel does, holds them until every prerequisite grid has completed and its memory is visible, and
+// then lets the successor's launch overlap this grid.  Launched plainly, the prologue is a no-op.
+// What it buys is launch latency between small dependent kernels (the 13 launches of a query ordering,
+// the two kernels of an ICP iteration); it must not be used where the waiting blocks would take slots a
+// full-device predecessor still needs (callers decide).
+__device__ __forceinline__ void pdl_prologue() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t s, bool pdl, Args&&... args) {
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---- exact arithmetic helpers (identical results on host and device)
 PCNN_HD double dmul(double a, double b) {
 #if defined(__CUDA_ARCH__)

@@ -94,18 +94,6 @@ struct PeerView {
 
 namespace pcnn {
 
-// Programmatic dependent launch: the two kernels of an iteration are launched with
-// cudaLaunchAttributeProgrammaticStreamSerialization, so the NEXT kernel's blocks may become resident
-// while this grid still runs; `griddepcontrol.wait` holds them until every prerequisite grid has
-// completed and its memory is visible (nothing of the predecessor is read before it), and
-// `launch_dependents` lets the successor's launch overlap this grid from its first instruction.
-// Without the launch attribute both are no-ops.  What it buys: the launch gap between the kernels,
-// which is 10-20 % of a 19 us converged iteration at 100k points.
-__device__ __forceinline__ void pdl_wait_and_release() {
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-}
-
 __device__ __forceinline__ void xform(const float* R, const float* t, float& x, float& y, float& z) {
     // ((r0*x + r1*y) + r2*z) + t, float32, no FMA: transformCloudInplace, registration.cpp:165-178
     const float nx = fadd(fadd(fadd(fmul(R[0], x), fmul(R[1], y)), fmul(R[2], z)), t[0]);
@@ -351,7 +339,7 @@ icp_search_kernel(IndexView iv, float4* cur, int* prev, int* prev2, float4* cert
     __shared__ float s_move[ICP_J * ICP_THREADS];           // how far T_delta moved the point
     __shared__ unsigned s_co_stack[ICP_THREADS / 32][CO_STACK];  // nn1_coop: one query, the whole warp
     __shared__ unsigned s_co_gl[ICP_THREADS / 32][CO_GLIST];
-    pdl_wait_and_release();
+    pdl_prologue();  // launched with programmatic stream serialization when the grid leaves room (pcnn_common.cuh)
     if (st->done) return;  // uniform: loop already ended (converged / failed)
     int walked_here = 0;
     const float move_max = move_frac * __ldg(iv.cube + 8);
@@ -531,7 +519,7 @@ icp_accumulate_kernel(IndexView iv, const float4* cur, const float4* __restrict_
     __shared__ double s_part[ICP_THREADS / 32][ICP_NS];
     __shared__ long long s_last[ICP_THREADS / 32];
     __shared__ bool s_is_last;
-    pdl_wait_and_release();
+    pdl_prologue();  // launched with programmatic stream serialization when the grid leaves room (pcnn_common.cuh)
     if (st->done) return;  // uniform: loop already ended (converged / failed)
 #ifdef PCNN_ICP_TIMING
     if (blockIdx.x == 0 && threadIdx.x == 0) {

@@ -447,6 +447,9 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
     } else if (!std::strcmp(name, "nvtx")) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: nvtx must be 0 or 1");
         index->opt_nvtx = value;
+    } else if (!std::strcmp(name, "pdl")) {
+        PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: pdl must be 0 or 1");
+        index->opt_pdl = value;
     } else if (!std::strcmp(name, "icp_pdl")) {
         PCNN_CHECK_ARG(value == 0 || value == 1, "pcnn_set_option: icp_pdl must be 0 or 1");
         index->opt_icp_pdl = value;

@@ -41,6 +41,7 @@ struct pcnn_index {
     unsigned long long* dbg_warp_times = nullptr;  // diagnostics (pcnn_debug_warp_times)
     int opt_profile = 0;
     int opt_nvtx = 0;           // 1: host-side NVTX ranges around the phases of every call on this handle (pcnn.knn.order, ...)
+    int opt_pdl = 1;            // query ordering + kNN search launched with programmatic stream serialization
     int opt_icp_pdl = 1;        // ICP: programmatic dependent launch between the kernels of an iteration
     int opt_icp_cert = 1;       // ICP correspondence certificates (pcnn_icp.cu); 0 = search every point every iteration
     cudaEvent_t prof0 = nullptr, prof1 = nullptr;  // bracket the last main search kernel

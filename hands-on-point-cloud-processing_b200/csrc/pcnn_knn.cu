@@ -25,6 +25,7 @@ namespace pcnn {
 __global__ void query_code_kernel(const float* __restrict__ q, int nq, int stride,
                                   const float* __restrict__ cube, int bits, unsigned* __restrict__ codes,
                                   unsigned* __restrict__ perm) {
+    pdl_prologue();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nq) return;
     const float* p = q + (size_t)i * stride;
@@ -43,8 +44,9 @@ int sort_queries(const pcnn_index* ix, const float* q, int64_t nq, int stride, u
     PCNN_CUDA(sc.get(&p1, (size_t)n));
     PCNN_CUDA(sc.get(&hist, radix_hist_elems(n)));
     const int bits = ix->opt_sort_bits;
-    query_code_kernel<<<(n + 255) / 256, 256, 0, s>>>(q, n, stride, ix->cube, bits, c0, p0);
-    int where = radix_sort_pairs<unsigned>(c0, p0, c1, p1, hist, n, bits, s);
+    const bool pdl = ix->opt_pdl != 0;
+    launch_pdl(query_code_kernel, dim3((n + 255) / 256), dim3(256), s, pdl, q, n, stride, (const float*)ix->cube, bits, c0, p0);
+    int where = radix_sort_pairs<unsigned>(c0, p0, c1, p1, hist, n, bits, s, pdl);
     *perm_out = where ? p1 : p0;
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
@@ -689,6 +691,7 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                unsigned long long* __restrict__ dbg) {
     __shared__ int s_qg[KQ_DEPTH][KT_THREADS];
     __shared__ float s_ql[KQ_DEPTH][KT_THREADS];
+    pdl_prologue();
     const unsigned full = 0xffffffffu;
     const int tid = threadIdx.x;
     const int t = blockIdx.x * KT_THREADS + tid;
@@ -1502,8 +1505,8 @@ static void launch_lockstep_k(const pcnn_index* ix, const float* q, int nq, int 
 template <int K>
 static void launch_dfs_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
                          int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
-    knn_dfs_kernel<K><<<(nq + KT_THREADS - 1) / KT_THREADS, KT_THREADS, 0, s>>>(
-        ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
+    launch_pdl(knn_dfs_kernel<K>, dim3((nq + KT_THREADS - 1) / KT_THREADS), dim3(KT_THREADS), s, ix->opt_pdl != 0 && perm != nullptr,
+               ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
 }
 #ifdef PCNN_STUDY
 template <int K>

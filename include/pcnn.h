@@ -144,6 +144,8 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
  * same sets.
  * `icp_certificates` (default 1): 0 makes the ICP loop search every source point in every
  * iteration; the result is the same bit for bit (tests/test_gpu_configs.py), only slower.
+ * `pdl` (default 1): the query ordering of pcnn_knn and the search kernel behind it are launched with
+ * programmatic stream serialization (each launch overlaps its predecessor's tail); 0 = plain launches.
  * `icp_pdl` (default 1): the two kernels of an ICP iteration are launched with programmatic
  * stream serialization (the successor's launch overlaps the predecessor) when the source cloud does
  * not fill the device; 0 = plain launches.  Same result either way.

@@ -19,3 +19,13 @@ for K in [int(x) for x in os.environ.get("KS", "8").split(",")]:
         best = min(best, ix.last_kernel_ms())
     chk = int((idx.to(torch.int64) * torch.arange(1, K + 1, device=dev)).sum().item()) ^ int(dist.view(torch.int64).sum().item())
     print("k=%d kernel %.4f ms  %.1f M q/s  checksum %x" % (K, best, len(qry) / best / 1e3, chk & 0xffffffffffff), flush=True)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+for pdl in (0, 1, 0, 1):
+    ix.set_option("pdl", pdl)
+    best = 1e9
+    for _ in range(8):
+        torch.cuda.synchronize(); e0.record()
+        ix.knn(dq, 8, dist="f32")
+        e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    print("pdl=%d: whole device-resident call (ordering + search) %.4f ms, search kernel %.4f ms" % (pdl, best, ix.last_kernel_ms()), flush=True)

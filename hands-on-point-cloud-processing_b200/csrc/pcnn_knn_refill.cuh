@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(KT_THREADS, K <= 8 ? PCNN_DFS_MINBLOCKS : PCNN
 knn_dfs_refill_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                       const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
                       float* __restrict__ out_dist, double* __restrict__ out_dist64,
-                      unsigned* __restrict__ next_query, int refill_min) {
+                      unsigned* __restrict__ next_query, int refill_min, int chunk) {
     __shared__ int s_qg[KQ_DEPTH][KT_THREADS];
     __shared__ float s_ql[KQ_DEPTH][KT_THREADS];
     const unsigned full = 0xffffffffu;
@@ -43,18 +43,33 @@ knn_dfs_refill_kernel(IndexView iv, const float* __restrict__ q, int nq, int str
     unsigned pending = 0;
     bool done = true, fresh = false;
     bool drained = false;     // the global counter has run past the batch
+    // chunk > 0: no global counter -- every warp owns `chunk` consecutive queries of the (Morton-ordered)
+    // batch and its lanes refill from that chunk only, so a lane that joins late is still a neighbour of
+    // the lanes that are walking
+    const long long wfirst = (long long)(blockIdx.x * (KT_THREADS / 32) + (tid >> 5)) * chunk;
+    const int wcount = chunk > 0 ? (int)((wfirst >= nq) ? 0 : ((nq - wfirst) < chunk ? (nq - wfirst) : chunk)) : 0;
+    int wnext = 0;
+    if (chunk > 0 && wcount == 0) return;  // warp-uniform
     int ins_dummy = 0;
     while (true) {
         // ---- (A) refill: lanes without a query fetch the next ones together
         const unsigned idle = __ballot_sync(full, qi < 0);
         if (!drained && (idle == full || __popc(idle) >= refill_min)) {
             unsigned base = 0;
-            if (lane == 0) base = atomicAdd(next_query, (unsigned)__popc(idle));
-            base = __shfl_sync(full, base, 0);
-            if (base + (unsigned)__popc(idle) >= (unsigned)nq) drained = true;
+            unsigned limit = (unsigned)nq;
+            if (chunk > 0) {
+                base = (unsigned)(wfirst + wnext);
+                limit = (unsigned)(wfirst + wcount);
+                wnext += __popc(idle);
+                if (wnext >= wcount) drained = true;
+            } else {
+                if (lane == 0) base = atomicAdd(next_query, (unsigned)__popc(idle));
+                base = __shfl_sync(full, base, 0);
+                if (base + (unsigned)__popc(idle) >= (unsigned)nq) drained = true;
+            }
             if (qi < 0) {
                 const unsigned mine = base + (unsigned)__popc(idle & lt);
-                if (mine < (unsigned)nq) {
+                if (mine < limit) {
                     qi = perm ? (int)perm[mine] : (int)mine;
                     const float* qp = q + (size_t)qi * stride;
                     qxf = qp[0]; qyf = qp[1]; qzf = qp[2];

@@ -11,6 +11,8 @@ pts, nrm, qry = bench.make_clouds(0)
 dev = torch.device("cuda", 0)
 ix = pc.Index(torch.from_numpy(pts).to(dev))
 ix.set_option("profile", 1)
+if os.environ.get("METHOD"):  # a study variant (PCNN_LIB=.../libpcnn_study.so)
+    ix.set_option("method", int(os.environ["METHOD"]))
 dq = torch.from_numpy(qry).to(dev)
 for K in [int(x) for x in os.environ.get("KS", "8").split(",")]:
     best = 1e9
@@ -20,7 +22,7 @@ for K in [int(x) for x in os.environ.get("KS", "8").split(",")]:
     chk = int((idx.to(torch.int64) * torch.arange(1, K + 1, device=dev)).sum().item()) ^ int(dist.view(torch.int64).sum().item())
     print("k=%d kernel %.4f ms  %.1f M q/s  checksum %x" % (K, best, len(qry) / best / 1e3, chk & 0xffffffffffff), flush=True)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-for pdl in (0, 1, 0, 1):
+for pdl in ((0, 1, 0, 1) if not os.environ.get("METHOD") else ()):
     ix.set_option("pdl", pdl)
     best = 1e9
     for _ in range(8):

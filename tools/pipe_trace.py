@@ -17,3 +17,5 @@ for it in range(int(os.environ.get("ITERS", "4"))):
     t0 = time.perf_counter()
     ix.knn(h_q, K, out=(h_idx, h_dist))
     print("call %d: %.3f ms" % (it, 1e3 * (time.perf_counter() - t0)), file=sys.stderr, flush=True)
+chk = int((torch.from_numpy(h_idx).to(torch.int64) * torch.arange(1, K + 1)).sum().item()) ^ int(torch.from_numpy(h_dist).view(torch.int32).to(torch.int64).sum().item())
+print("checksum %x" % (chk & 0xffffffffffff), file=sys.stderr, flush=True)

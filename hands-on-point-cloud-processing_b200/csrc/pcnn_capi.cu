@@ -130,6 +130,10 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
             q0 = 32768 + 65536;
         }
         for (; q0 < nq; q0 += chunk) plan.push_back({q0, std::min<int64_t>(chunk, nq - q0), 0});
+#ifdef PCNN_STUDY
+        if (const char* ev = std::getenv("PCNN_HOST_LEAD_SORT"))  // tuning aid: order the queries of the first stages
+            for (int i = 0; i < std::atoi(ev) && i < (int)plan.size(); i++) plan[i].sort = 1;
+#endif
     }
     int max_streams = HOST_STREAMS;
 #ifdef PCNN_STUDY

@@ -367,6 +367,125 @@ __device__ __forceinline__ void scan_own_group(const IndexView& iv, int g, bool 
     }
 }
 
+// ------------------------------------------------------------------ the k best as (float key, position)
+// knn_dfs_kernel's list.  The order is still the reference's -- ascending exact double key, ties by original
+// index (resultSet.hpp:65-91 via kless) -- but an entry is two registers, not three, and a comparison is one
+// FSETP: an entry carries f = ru32(key), the double key rounded UP to float32, and the point's POSITION in
+// the Morton-ordered array.  Rounding is monotone, so f_a < f_b implies key_a < key_b; only when two floats
+// are EQUAL (keys within one float32 ulp of each other, or true ties) are the double keys and the original
+// indices recomputed from the two points and compared exactly (cold path).  The row's indices and distances
+// are recomputed from the positions when the walk has ended.  f of the k-th entry is at once the float32
+// pruning bound the walk needs (an upper bound of the k-th key).
+template <int K>
+struct TopKf {
+    float key[K];
+    int pos[K];
+    __device__ __forceinline__ void init() {
+#pragma unroll
+        for (int j = 0; j < K; j++) { key[j] = __int_as_float(0x7f800000); pos[j] = -1; }
+    }
+};
+
+// exact order of two entries whose float keys are equal (an empty slot is greater than everything)
+__device__ __noinline__ bool entry_less_exact(const float4* __restrict__ pts, int pa, int pb, double qx, double qy,
+                                              double qz) {
+    if (pa < 0) return false;
+    if (pb < 0) return true;
+    const float4 a = __ldg(pts + pa), b = __ldg(pts + pb);
+    return kless(key64(a.x, a.y, a.z, qx, qy, qz), __float_as_int(a.w), key64(b.x, b.y, b.z, qx, qy, qz),
+                 __float_as_int(b.w));
+}
+
+// candidate (f, ppos) against the list; returns true if it went in
+template <int K>
+__device__ __forceinline__ bool topkf_offer(TopKf<K>& tk, float f, int ppos, const float4* __restrict__ pts,
+                                            double qx, double qy, double qz) {
+    if (f > tk.key[K - 1]) return false;
+    bool tie = false;
+#pragma unroll
+    for (int m = 0; m < K; m++) tie |= (f == tk.key[m]);
+    if (!tie) {
+        // f < key[K-1]: it goes in.  c(m) = "new < entry m" is monotone in m; entry j becomes entry j-1 where
+        // c(j-1) holds, the new one where c(j) holds and c(j-1) does not, and stays otherwise.
+#pragma unroll
+        for (int j = K - 1; j > 0; --j) {
+            const bool cj = f < tk.key[j], cjm = f < tk.key[j - 1];
+            tk.key[j] = cjm ? tk.key[j - 1] : (cj ? f : tk.key[j]);
+            tk.pos[j] = cjm ? tk.pos[j - 1] : (cj ? ppos : tk.pos[j]);
+        }
+        if (f < tk.key[0]) { tk.key[0] = f; tk.pos[0] = ppos; }
+        return true;
+    }
+    // cold: some float key equals f -- bubble the candidate down with exact comparisons where floats tie
+    if (!(f < tk.key[K - 1] || entry_less_exact(pts, ppos, tk.pos[K - 1], qx, qy, qz))) return false;
+    tk.key[K - 1] = f;
+    tk.pos[K - 1] = ppos;
+#pragma unroll
+    for (int j = K - 1; j > 0; --j) {
+        const float ka = tk.key[j - 1], kb = tk.key[j];
+        const int pa = tk.pos[j - 1], pb = tk.pos[j];
+        bool sw = kb < ka;
+        if (kb == ka) sw = entry_less_exact(pts, pb, pa, qx, qy, qz);
+        tk.key[j - 1] = sw ? kb : ka;
+        tk.pos[j - 1] = sw ? pb : pa;
+        tk.key[j] = sw ? ka : kb;
+        tk.pos[j] = sw ? pa : pb;
+    }
+    return true;
+}
+
+template <int K>
+__device__ __forceinline__ void scan_own_group_f(const IndexView& iv, int g, bool active, float qxf, float qyf,
+                                                 float qzf, double qx, double qy, double qz, TopKf<K>& tk,
+                                                 float& wf, int& ins_rounds) {
+    const unsigned full = 0xffffffffu;
+    const int first = g << PCNN_GROUP_LOG;
+    unsigned pass = 0;
+    if (active) {
+        const int cnt = (iv.n - first) < PCNN_GROUP ? (iv.n - first) : PCNN_GROUP;
+#pragma unroll
+        for (int j = 0; j < PCNN_GROUP; j++) {
+            if (j < cnt) {
+                const float4 p = __ldg(iv.pts + first + j);
+                const float lbf = lbsq32(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
+                if (!(lbf > wf)) pass |= 1u << j;
+            }
+        }
+    }
+    while (__any_sync(full, pass != 0)) {
+        ins_rounds++;
+        if (pass) {
+            const int j = __ffs((int)pass) - 1;
+            pass &= pass - 1;
+            const float4 p = __ldg(iv.pts + first + j);
+            const float f = ru32(key64(p.x, p.y, p.z, qx, qy, qz));
+            if (topkf_offer<K>(tk, f, first + j, iv.pts, qx, qy, qz)) wf = fminf(wf, tk.key[K - 1]);
+        }
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void write_row_f(const TopKf<K>& tk, const float4* __restrict__ pts, double qx, double qy,
+                                            double qz, int64_t row, int k, int32_t* out_idx, float* out_dist,
+                                            double* out_dist64) {
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+        if (j < k) {
+            const bool have = tk.pos[j] >= 0;
+            double d = PCNN_INF_D;
+            int id = -1;
+            if (have) {
+                const float4 p = __ldg(pts + tk.pos[j]);
+                d = sqrt(key64(p.x, p.y, p.z, qx, qy, qz));  // IEEE sqrt, as the reference stores it
+                id = __float_as_int(p.w);
+            }
+            out_idx[row * k + j] = id;
+            if (out_dist) out_dist[row * k + j] = (float)d;
+            if (out_dist64) out_dist64[row * k + j] = d;
+        }
+    }
+}
+
 #ifdef PCNN_STUDY  // measured-slower variant kept for study: not in the shipped library
 template <int K>
 __global__ void __launch_bounds__(KT_THREADS)
@@ -711,7 +830,7 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     const float* qp = q + (size_t)qi * stride;
     const float qxf = qp[0], qyf = qp[1], qzf = qp[2];
     const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
-    TopK<K> tk;
+    TopKf<K> tk;
     tk.init();
     int c_round = 0, c_scan = 0, c_ins = 0, c_steps = 0;  // diagnostics
     if (iv.n > 0) {
@@ -733,7 +852,7 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
             const int maxc = __reduce_max_sync(full, cnt);
             for (int r = 0; r < maxc; r++) {
                 const bool act = r < cnt;
-                scan_own_group<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
+                scan_own_group_f<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
             }
             cnt = 0;
         }
@@ -811,7 +930,7 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                 for (int r = 0; r < maxc; r++) {
                     const bool act = r < cnt && !(s_ql[r][tid] > wf);
                     if (__any_sync(full, act)) {
-                        scan_own_group<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
+                        scan_own_group_f<K>(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
                         c_scan++;
                     }
                 }
@@ -820,7 +939,7 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
             if (!__any_sync(full, !done)) break;
         }
     }
-    if (live) write_row<K>(tk, qi, k, out_idx, out_dist, out_dist64);
+    if (live) write_row_f<K>(tk, iv.pts, qx, qy, qz, qi, k, out_idx, out_dist, out_dist64);
     if (dbg) {
         const int maxsteps = __reduce_max_sync(full, c_steps);
         const int sumsteps = __reduce_add_sync(full, c_steps);

@@ -1157,41 +1157,48 @@ constexpr int KH_CAP = 32;
 #endif
 constexpr int KH_QDEPTH = PCNN_KH_QDEPTH;  // queue entries per lane in the heap kernel (shared memory decides its occupancy)
 
+// Entries are (float32 key rounded up, position in the Morton-ordered array) as in TopKf: 8 bytes instead
+// of 12, one FSETP per comparison, exact double keys + original indices only where two floats are equal.
 struct HeapRef {
-    double* key;  // [KH_CAP][KH_THREADS], this lane's column
-    int* idx;
+    float* key;  // [KH_CAP][KH_THREADS], this lane's column
+    int* pos;
     int k;
-    __device__ __forceinline__ double& K(int i) const { return key[i * KH_THREADS]; }
-    __device__ __forceinline__ int& I(int i) const { return idx[i * KH_THREADS]; }
+    const float4* pts;
+    double qx, qy, qz;
+    __device__ __forceinline__ float& K(int i) const { return key[i * KH_THREADS]; }
+    __device__ __forceinline__ int& I(int i) const { return pos[i * KH_THREADS]; }
     __device__ __forceinline__ void init() const {
-        for (int i = 0; i < k; i++) { K(i) = __longlong_as_double(0x7ff0000000000000LL); I(i) = 0x7fffffff; }
+        for (int i = 0; i < k; i++) { K(i) = __int_as_float(0x7f800000); I(i) = -1; }
     }
-    __device__ __forceinline__ bool accepts(double d, int id) const { return kless(d, id, K(0), I(0)); }
-    // place (d, id) at position i of a heap of size n and sift it down
-    __device__ __forceinline__ void sift(int i, int n, double d, int id) const {
+    __device__ __forceinline__ bool less(float fa, int pa, float fb, int pb) const {
+        return fa < fb || (fa == fb && entry_less_exact(pts, pa, pb, qx, qy, qz));
+    }
+    __device__ __forceinline__ bool accepts(float f, int p) const { return less(f, p, K(0), I(0)); }
+    // place (f, p) at position i of a heap of size n and sift it down
+    __device__ __forceinline__ void sift(int i, int n, float f, int p) const {
         while (true) {
             int c = 2 * i + 1;
             if (c >= n) break;
-            double ck = K(c);
+            float ck = K(c);
             int ci = I(c);
             if (c + 1 < n) {
-                const double rk = K(c + 1);
+                const float rk = K(c + 1);
                 const int ri = I(c + 1);
-                if (kless(ck, ci, rk, ri)) { ck = rk; ci = ri; c = c + 1; }
+                if (less(ck, ci, rk, ri)) { ck = rk; ci = ri; c = c + 1; }
             }
-            if (!kless(d, id, ck, ci)) break;
+            if (!less(f, p, ck, ci)) break;
             K(i) = ck;
             I(i) = ci;
             i = c;
         }
-        K(i) = d;
-        I(i) = id;
+        K(i) = f;
+        I(i) = p;
     }
-    __device__ __forceinline__ void replace_root(double d, int id) const { sift(0, k, d, id); }
+    __device__ __forceinline__ void replace_root(float f, int p) const { sift(0, k, f, p); }
     // heap -> ascending order in place
     __device__ __forceinline__ void sort() const {
         for (int n = k - 1; n > 0; n--) {
-            const double lk = K(n);
+            const float lk = K(n);
             const int li = I(n);
             K(n) = K(0);
             I(n) = I(0);
@@ -1222,11 +1229,10 @@ __device__ __forceinline__ void scan_own_group_heap(const IndexView& iv, int g, 
             const int j = __ffs((int)pass) - 1;
             pass &= pass - 1;
             const float4 p = __ldg(iv.pts + first + j);
-            const double d = key64(p.x, p.y, p.z, qx, qy, qz);
-            const int id = __float_as_int(p.w);
-            if (hp.accepts(d, id)) {
-                hp.replace_root(d, id);
-                wf = fminf(wf, ru32(hp.K(0)));
+            const float f = ru32(key64(p.x, p.y, p.z, qx, qy, qz));
+            if (hp.accepts(f, first + j)) {
+                hp.replace_root(f, first + j);
+                wf = fminf(wf, hp.K(0));
             }
         }
     }
@@ -1236,7 +1242,7 @@ __global__ void __launch_bounds__(KH_THREADS)
 knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                     const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
                     float* __restrict__ out_dist, double* __restrict__ out_dist64) {
-    __shared__ double s_hk[KH_CAP][KH_THREADS];
+    __shared__ float s_hk[KH_CAP][KH_THREADS];
     __shared__ int s_hi[KH_CAP][KH_THREADS];
     __shared__ int s_qg[KH_QDEPTH][KH_THREADS];
     __shared__ float s_ql[KH_QDEPTH][KH_THREADS];
@@ -1251,8 +1257,10 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
     const double qx = (double)qxf, qy = (double)qyf, qz = (double)qzf;
     HeapRef hp;
     hp.key = &s_hk[0][tid];
-    hp.idx = &s_hi[0][tid];
+    hp.pos = &s_hi[0][tid];
     hp.k = k;
+    hp.pts = iv.pts;
+    hp.qx = qx; hp.qy = qy; hp.qz = qz;
     hp.init();
     if (iv.n > 0) {
         const float INFf = __int_as_float(0x7f800000);
@@ -1359,10 +1367,15 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
     hp.sort();
     if (live) {
         for (int j = 0; j < k; j++) {
-            const int id = hp.I(j);
-            const bool have = id != 0x7fffffff;
-            const double d = have ? sqrt(hp.K(j)) : hp.K(j);
-            out_idx[(size_t)qi * k + j] = have ? id : -1;
+            const int pj = hp.I(j);
+            double d = PCNN_INF_D;
+            int id = -1;
+            if (pj >= 0) {
+                const float4 p = __ldg(iv.pts + pj);
+                d = sqrt(key64(p.x, p.y, p.z, qx, qy, qz));  // IEEE sqrt, as the reference stores it
+                id = __float_as_int(p.w);
+            }
+            out_idx[(size_t)qi * k + j] = id;
             if (out_dist) out_dist[(size_t)qi * k + j] = (float)d;
             if (out_dist64) out_dist64[(size_t)qi * k + j] = d;
         }

@@ -165,6 +165,17 @@ PCNN_HD float lbsq32(float ax, float ay, float az) {
     return (float)(s * 0.9999980926513672);  // extra margin covers the host's round-to-nearest
 #endif
 }
+#if defined(__CUDACC__)
+// The same bound without the safety factor and with fused multiply-adds, for the kNN walks: three
+// instructions instead of six.  Every operation rounds DOWN, so the result s is <= the real
+// ax^2 + ay^2 + az^2, and the exact double key of any point the inputs bound is >= that real value
+// * (1 - 2^-50).  If s > wf in float32 then s >= wf * (1 + 2^-23), so key >= s * (1 - 2^-50) > wf
+// >= the k-th key: the candidate (or the whole box) is out, ties included -- no float lies in
+// [s * (1 - 2^-50), s), so a key EQUAL to the k-th never sees s > wf.  No margin is needed.
+__device__ __forceinline__ float lbsq32x(float ax, float ay, float az) {
+    return __fmaf_rd(az, az, __fmaf_rd(ay, ay, __fmul_rd(ax, ax)));
+}
+#endif
 // |a - b| rounded toward zero (never above the real difference)
 PCNN_HD float absdiff_rz(float a, float b) {
 #if defined(__CUDA_ARCH__)

@@ -447,7 +447,7 @@ __device__ __forceinline__ void scan_own_group_f(const IndexView& iv, int g, boo
         for (int j = 0; j < PCNN_GROUP; j++) {
             if (j < cnt) {
                 const float4 p = __ldg(iv.pts + first + j);
-                const float lbf = lbsq32(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
+                const float lbf = lbsq32x(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
                 if (!(lbf > wf)) pass |= 1u << j;
             }
         }
@@ -890,13 +890,13 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                         const int cl = (int)(((long long)iv.n0 + (1LL << L) - 1) >> L);
                         const float4* b = iv.box + 2 * ((size_t)iv.lev_off[L] + P);
                         const float4 alo = __ldg(b), ahi = __ldg(b + 1);
-                        const float lbA = lbsq32(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
+                        const float lbA = lbsq32x(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
                                                  boxgap_rd(alo.z, ahi.z, qzf));
                         float lbB = INFf;
                         const bool hasB = P + 1 < cl;
                         if (hasB) {
                             const float4 blo = __ldg(b + 2), bhi = __ldg(b + 3);
-                            lbB = lbsq32(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
+                            lbB = lbsq32x(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
                                          boxgap_rd(blo.z, bhi.z, qzf));
                         }
                         if (mode == 0) {
@@ -1219,7 +1219,7 @@ __device__ __forceinline__ void scan_own_group_heap(const IndexView& iv, int g, 
         for (int j = 0; j < PCNN_GROUP; j++) {
             if (j < cnt) {
                 const float4 p = __ldg(iv.pts + first + j);
-                const float lbf = lbsq32(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
+                const float lbf = lbsq32x(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
                 if (!(lbf > wf)) pass |= 1u << j;
             }
         }
@@ -1317,13 +1317,13 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
                         const int cl = (int)(((unsigned)iv.n0 + (1u << L) - 1u) >> L);
                         const float4* b = iv.box + 2 * ((size_t)iv.lev_off[L] + P);
                         const float4 alo = __ldg(b), ahi = __ldg(b + 1);
-                        const float lbA = lbsq32(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
+                        const float lbA = lbsq32x(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
                                                  boxgap_rd(alo.z, ahi.z, qzf));
                         float lbB = INFf;
                         const bool hasB = P + 1 < cl;
                         if (hasB) {
                             const float4 blo = __ldg(b + 2), bhi = __ldg(b + 3);
-                            lbB = lbsq32(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
+                            lbB = lbsq32x(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
                                          boxgap_rd(blo.z, bhi.z, qzf));
                         }
                         if (mode == 0) {

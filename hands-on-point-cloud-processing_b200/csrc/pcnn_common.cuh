@@ -158,7 +158,7 @@ inline float i2f_host_next(float f) { return nextafterf(f, HUGE_VALF); }
 // (or every point of the box) cannot enter the list -- ties included.  Cheap: FP32 pipe only.
 PCNN_HD float lbsq32(float ax, float ay, float az) {
 #if defined(__CUDA_ARCH__)
-    const float s = __fadd_rd(__fadd_rd(__fmul_rd(ax, ax), __fmul_rd(ay, ay)), __fmul_rd(az, az));
+    const float s = __fmaf_rd(az, az, __fmaf_rd(ay, ay, __fmul_rd(ax, ax)));  // every step rounds down: s <= the real sum
     return __fmul_rd(s, 0.99999905f);
 #else
     const double s = (double)ax * ax + (double)ay * ay + (double)az * az;

@@ -89,7 +89,7 @@ int sort_queries_fine(const pcnn_index* ix, const float* q, int64_t nq, int stri
 }
 
 // ------------------------------------------------------------------ thread-per-query
-constexpr int KT_THREADS = 128;
+[[maybe_unused]] constexpr int KT_THREADS = 128;
 #ifndef PCNN_DFS_MINBLOCKS
 #define PCNN_DFS_MINBLOCKS 8  // resident blocks per SM asked of ptxas for knn_dfs_kernel (64 registers; measured)
 #endif
@@ -807,18 +807,27 @@ knn_lockstep_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
 // curve where the Morton neighbours are not the spatial ones.  The warp runs the 32 walks in
 // lock step (fixed rounds of predicated steps), groups a lane needs go to its queue and the
 // queues are drained together, as in knn_lockstep_kernel.
+// levels whose deferred siblings have their lower bound remembered (per lane, shared memory); a sibling
+// deferred higher up (clouds beyond 2^27 points) is simply visited
+constexpr int KW_PLEVELS = 24;
+#ifndef PCNN_KD_THREADS
+#define PCNN_KD_THREADS 128
+#endif
+constexpr int KD_THREADS = PCNN_KD_THREADS;  // threads per block of knn_dfs_kernel
+
 template <int K>
-__global__ void __launch_bounds__(KT_THREADS, K <= 8 ? PCNN_DFS_MINBLOCKS : PCNN_DFS_MINBLOCKS16)
+__global__ void __launch_bounds__(KD_THREADS, (K <= 8 ? PCNN_DFS_MINBLOCKS : PCNN_DFS_MINBLOCKS16) * (128 / KD_THREADS))
 knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                const unsigned* __restrict__ perm, int k, int32_t* __restrict__ out_idx,
                float* __restrict__ out_dist, double* __restrict__ out_dist64,
                unsigned long long* __restrict__ dbg) {
-    __shared__ int s_qg[KQ_DEPTH][KT_THREADS];
-    __shared__ float s_ql[KQ_DEPTH][KT_THREADS];
+    __shared__ int s_qg[KQ_DEPTH][KD_THREADS];
+    __shared__ float s_ql[KQ_DEPTH][KD_THREADS];
+    __shared__ float s_pl[KW_PLEVELS][KD_THREADS];
     pdl_prologue();
     const unsigned full = 0xffffffffu;
     const int tid = threadIdx.x;
-    const int t = blockIdx.x * KT_THREADS + tid;
+    const int t = blockIdx.x * KD_THREADS + tid;
     unsigned long long dbg_t0 = 0, dbg_c0 = 0;
     if (dbg) {
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
@@ -868,59 +877,59 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                 const bool can = !done && cnt <= KQ_DEPTH - 2 && !(cnt > 0 && wf > 3.0e38f);
                 if (!__any_sync(full, can)) break;
                 if (can) {
-                    int L, P, far = 0;
-                    if (mode == 0) {
-                        L = l - 1;
-                        P = 2 * n;
-                    } else if (pending == 0) {
-                        done = true;
-                        L = 0;
-                        P = 0;
-                    } else {
-                        const int lp = __ffs((int)pending) - 1;
-                        pending &= pending - 1;
-                        far = (n >> (lp - l)) ^ 1;
-                        l = lp;
-                        n = far;
-                        L = lp;
-                        P = far & ~1;
+                    if (mode != 0) {
+                        // backtrack: the nearest deferred sibling whose remembered bound still beats the k-th
+                        // key (no load, no box test: the bound was computed when the sibling was deferred)
+                        mode = 2;
+                        while (pending != 0) {
+                            const int lp = __ffs((int)pending) - 1;
+                            pending &= pending - 1;
+                            const float lbp = lp < KW_PLEVELS ? s_pl[lp][tid] : 0.f;
+                            if (!(lbp > wf)) {
+                                n = (n >> (lp - l)) ^ 1;
+                                l = lp;
+                                mode = 0;
+                                break;
+                            }
+                        }
+                        if (mode != 0) done = true;
                     }
                     if (!done) {
+                        // examine the two children of (l, n)
                         c_steps++;
-                        const int cl = (int)(((long long)iv.n0 + (1LL << L) - 1) >> L);
+                        const int L = l - 1, P = 2 * n;
+                        const int cl = (int)(((unsigned)iv.n0 + (1u << L) - 1u) >> L);
                         const float4* b = iv.box + 2 * ((size_t)iv.lev_off[L] + P);
                         const float4 alo = __ldg(b), ahi = __ldg(b + 1);
                         const float lbA = lbsq32x(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
-                                                 boxgap_rd(alo.z, ahi.z, qzf));
+                                                  boxgap_rd(alo.z, ahi.z, qzf));
                         float lbB = INFf;
                         const bool hasB = P + 1 < cl;
                         if (hasB) {
                             const float4 blo = __ldg(b + 2), bhi = __ldg(b + 3);
                             lbB = lbsq32x(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
-                                         boxgap_rd(blo.z, bhi.z, qzf));
+                                          boxgap_rd(blo.z, bhi.z, qzf));
                         }
-                        if (mode == 0) {
-                            bool first1 = lbB < lbA;
-                            if (hasB && lbB == lbA)  // tie (query inside both boxes): follow the curve
-                                first1 = qcode >= __ldg(iv.gcode + ((size_t)(P + 1) << L));
-                            const float lbn = first1 ? lbB : lbA, lbf2 = first1 ? lbA : lbB;
-                            const int near = P + (first1 ? 1 : 0);
-                            const bool passN = !(lbn > wf);
-                            const bool passF = !(lbf2 > wf) && lbf2 < INFf;
-                            if (L == 0) {
-                                if (passN && (near < h0 || near > h1)) { s_qg[cnt][tid] = near; s_ql[cnt][tid] = lbn; cnt++; }
-                                if (passF && ((near ^ 1) < h0 || (near ^ 1) > h1)) { s_qg[cnt][tid] = near ^ 1; s_ql[cnt][tid] = lbf2; cnt++; }
-                                mode = 1;
-                            } else if (passN) {
-                                if (passF) pending |= 1u << L;
-                                l = L;
-                                n = near;
-                            } else {
-                                mode = 1;
+                        bool first1 = lbB < lbA;
+                        if (hasB && lbB == lbA)  // tie (query inside both boxes): follow the curve
+                            first1 = qcode >= __ldg(iv.gcode + ((size_t)(P + 1) << L));
+                        const float lbn = first1 ? lbB : lbA, lbf2 = first1 ? lbA : lbB;
+                        const int near = P + (first1 ? 1 : 0);
+                        const bool passN = !(lbn > wf);
+                        const bool passF = !(lbf2 > wf) && lbf2 < INFf;
+                        if (L == 0) {
+                            if (passN && (near < h0 || near > h1)) { s_qg[cnt][tid] = near; s_ql[cnt][tid] = lbn; cnt++; }
+                            if (passF && ((near ^ 1) < h0 || (near ^ 1) > h1)) { s_qg[cnt][tid] = near ^ 1; s_ql[cnt][tid] = lbf2; cnt++; }
+                            mode = 1;
+                        } else if (passN) {
+                            if (passF) {
+                                pending |= 1u << L;
+                                if (L < KW_PLEVELS) s_pl[L][tid] = lbf2;
                             }
+                            l = L;
+                            n = near;
                         } else {
-                            const float lbv = (far & 1) ? lbB : lbA;
-                            if (!(lbv > wf)) mode = 0;  // visit it: next step examines its children
+                            mode = 1;
                         }
                     }
                 }
@@ -1642,7 +1651,7 @@ static void launch_lockstep_k(const pcnn_index* ix, const float* q, int nq, int 
 template <int K>
 static void launch_dfs_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
                          int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
-    launch_pdl(knn_dfs_kernel<K>, dim3((nq + KT_THREADS - 1) / KT_THREADS), dim3(KT_THREADS), s, ix->opt_pdl != 0 && perm != nullptr,
+    launch_pdl(knn_dfs_kernel<K>, dim3((nq + KD_THREADS - 1) / KD_THREADS), dim3(KD_THREADS), s, ix->opt_pdl != 0 && perm != nullptr,
                ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
 }
 #ifdef PCNN_STUDY

@@ -807,6 +807,134 @@ knn_lockstep_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
 // curve where the Morton neighbours are not the spatial ones.  The warp runs the 32 walks in
 // lock step (fixed rounds of predicated steps), groups a lane needs go to its queue and the
 // queues are drained together, as in knn_lockstep_kernel.
+// ------------------------------------------------------------------ cooperative finish of a warp's last walks
+// A warp's time is that of its longest walk: on the 1M x 1M workload the mean warp takes 100 us, one in a
+// hundred 156 us and more, and the kernel's last 130 us belong to a few dozen such warps, each stepping one
+// or two lanes through a long walk (query in a sparse region) at the latency of one dependent load per step
+// (tools/warp_times.py).  When few lanes are left after KD_COOP_ROUNDS rounds, the warp stops stepping them
+// and finishes them one at a time with all 32 lanes: what is left of a lane's walk -- the node it stands on
+// and the deferred siblings whose remembered bound still beats the k-th key -- goes on a stack of nodes;
+// a node is replaced by its up to 32 descendants five levels down (one box per lane), a node of <= 32 points
+// is scanned one point per lane, survivors are keyed exactly in parallel and handed to the owner lane, which
+// inserts them.  The same points are offered as the lock-step walk would offer (the remaining subtrees, minus
+// the seed groups), so the list -- exact keys, ties by index -- ends up the same, whatever the order.
+// The stack lives in the warp's columns of the group queues, which are empty at a round boundary.
+#ifndef PCNN_KD_COOP_LANES
+#define PCNN_KD_COOP_LANES 4
+#endif
+#ifndef PCNN_KD_COOP_ROUNDS
+#define PCNN_KD_COOP_ROUNDS 8
+#endif
+constexpr int KD_COOP_LANES = PCNN_KD_COOP_LANES, KD_COOP_ROUNDS = PCNN_KD_COOP_ROUNDS;
+
+template <int K, int THREADS, int QDEPTH, int PLEVELS>
+__device__ __forceinline__ void knn_coop_finish(const IndexView& iv, unsigned todo, TopKf<K>& tk, float& wf, float qxf,
+                                                float qyf, float qzf, double qx, double qy, double qz, int l, int n,
+                                                unsigned pending, int mode, int h0, int h1,
+                                                int (*s_qg)[THREADS], float (*s_ql)[THREADS],
+                                                float (*s_pl)[THREADS]) {
+    static_assert(QDEPTH >= 4, "the warp's queue columns hold the node stack");
+    constexpr int CAP = (QDEPTH - 1) * 32;  // stack entries; the last row holds the candidates of a leaf
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x, lane = tid & 31, wb = tid & ~31;
+    const unsigned lt = (1u << lane) - 1u;
+#define KC_NODE(i) s_qg[(i) >> 5][wb + ((i) & 31)]
+#define KC_LB(i) s_ql[(i) >> 5][wb + ((i) & 31)]
+    while (todo) {
+        const int src = __ffs((int)todo) - 1;
+        todo &= todo - 1;
+        const float ox = __shfl_sync(full, qxf, src), oy = __shfl_sync(full, qyf, src), oz = __shfl_sync(full, qzf, src);
+        const int oh0 = __shfl_sync(full, h0, src), oh1 = __shfl_sync(full, h1, src);
+        float owf = __shfl_sync(full, wf, src);
+        int sp = 0;
+        if (lane == src) {
+            // deferred siblings, highest level first, so that the nearest one (lowest) is popped first
+            unsigned pm = pending;
+            while (pm) {
+                const int lp = 31 - __clz((int)pm);
+                pm &= ~(1u << lp);
+                const float lbp = lp < PLEVELS ? s_pl[lp][tid] : 0.f;
+                if (!(lbp > wf)) {
+                    KC_NODE(sp) = (int)(((unsigned)lp << 27) | (unsigned)((n >> (lp - l)) ^ 1));
+                    KC_LB(sp) = lbp;
+                    sp++;
+                }
+            }
+            if (mode == 0) {  // the node whose children were to be examined next
+                KC_NODE(sp) = (int)(((unsigned)l << 27) | (unsigned)n);
+                KC_LB(sp) = 0.f;
+                sp++;
+            }
+        }
+        sp = __shfl_sync(full, sp, src);
+        __syncwarp();
+        while (sp > 0) {
+            sp--;
+            const unsigned e = (unsigned)KC_NODE(sp);
+            const float elb = KC_LB(sp);
+            __syncwarp();
+            if (elb > owf) continue;  // the bound has fallen since the node was pushed
+            const int L = (int)(e >> 27), N = (int)(e & 0x7ffffffu);
+            if (L <= 2) {
+                // at most 32 points: one per lane
+                const int pi = ((N << L) << PCNN_GROUP_LOG) + lane;
+                const int g = pi >> PCNN_GROUP_LOG;
+                bool hit = false;
+                float f = 0.f;
+                if (lane < (PCNN_GROUP << L) && pi < iv.n && (g < oh0 || g > oh1)) {
+                    const float4 p = __ldg(iv.pts + pi);
+                    const float lbf = lbsq32x(absdiff_rz(p.x, ox), absdiff_rz(p.y, oy), absdiff_rz(p.z, oz));
+                    if (!(lbf > owf)) {
+                        f = ru32(key64(p.x, p.y, p.z, (double)ox, (double)oy, (double)oz));
+                        hit = !(f > owf);
+                    }
+                }
+                const unsigned hm = __ballot_sync(full, hit);
+                if (hm) {
+                    if (hit) {
+                        const int slot = CAP + __popc(hm & lt);
+                        KC_LB(slot) = f;
+                        KC_NODE(slot) = pi;
+                    }
+                    __syncwarp();
+                    if (lane == src) {
+                        const int nc = __popc(hm);
+                        for (int c = 0; c < nc; c++)
+                            if (topkf_offer<K>(tk, KC_LB(CAP + c), KC_NODE(CAP + c), iv.pts, qx, qy, qz))
+                                wf = fminf(wf, tk.key[K - 1]);
+                    }
+                    owf = __shfl_sync(full, wf, src);
+                }
+            } else {
+                // up to 32 descendants, one box per lane: five levels down while the stack has room for them
+                // (a binary step otherwise: depth-first, the stack then grows by at most one node per level)
+                const int d = (sp <= CAP - 32 - PCNN_MAX_LEVELS) ? (L - 5 >= 2 ? 5 : L - 2) : 1;
+                const int Lc = L - d;
+                const int idx = (N << d) + lane;
+                const int cl = (int)(((unsigned)iv.n0 + (1u << Lc) - 1u) >> Lc);
+                bool pass = false;
+                float lb = 0.f;
+                if (lane < (1 << d) && idx < cl) {
+                    const float4* b = iv.box + 2 * ((size_t)iv.lev_off[Lc] + idx);
+                    const float4 lo = __ldg(b), hi = __ldg(b + 1);
+                    lb = lbsq32x(boxgap_rd(lo.x, hi.x, ox), boxgap_rd(lo.y, hi.y, oy), boxgap_rd(lo.z, hi.z, oz));
+                    pass = !(lb > owf);
+                }
+                const unsigned pm = __ballot_sync(full, pass);
+                if (pass) {
+                    const int slot = sp + __popc(pm & lt);
+                    KC_NODE(slot) = (int)(((unsigned)Lc << 27) | (unsigned)idx);
+                    KC_LB(slot) = lb;
+                }
+                sp += __popc(pm);
+            }
+            __syncwarp();
+        }
+    }
+#undef KC_NODE
+#undef KC_LB
+}
+
 // levels whose deferred siblings have their lower bound remembered (per lane, shared memory); a sibling
 // deferred higher up (clouds beyond 2^27 points) is simply visited
 constexpr int KW_PLEVELS = 24;
@@ -945,7 +1073,13 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                 }
                 cnt = 0;
             }
-            if (!__any_sync(full, !done)) break;
+            const unsigned alive = __ballot_sync(full, !done);
+            if (alive == 0) break;
+            if (__popc(alive) <= KD_COOP_LANES && c_round >= KD_COOP_ROUNDS) {
+                knn_coop_finish<K, KD_THREADS, KQ_DEPTH, KW_PLEVELS>(iv, alive, tk, wf, qxf, qyf, qzf, qx, qy, qz, l, n, pending,
+                                                                     mode, h0, h1, s_qg, s_ql, s_pl);
+                break;
+            }
         }
     }
     if (live) write_row_f<K>(tk, iv.pts, qx, qy, qz, qi, k, out_idx, out_dist, out_dist64);

@@ -56,6 +56,10 @@ __device__ __forceinline__ void nn1_lockstep(const IndexView& iv, float qx, floa
     // up front by independent loads and only climb.  Slower both with many searches in flight, 570 vs
     // 500 us per 1M-point ICP iteration, and with a few hundred, 148 vs 122 us: every sibling that
     // passes costs a pop and a re-test, where the descent prunes most of them on the way down.)
+    // (Also measured and dropped here: knn_dfs_kernel's remembered bounds of deferred siblings, which turn
+    // the backtracking step into a pop-and-compare -- standalone 1-NN 0.501 -> 0.487 ms per 1M queries, but
+    // the ICP loops lose: 1M p2plane 177 -> 182 us per iteration, 100k 30.8 -> 32.3, with 8 KB more shared
+    // memory per block and a data-dependent loop inside the step.)
     int l = walk_start_level(iv, seed_group, qx, qy, qz, best.bound());
     int n = seed_group >> l;
     unsigned pending = 0;

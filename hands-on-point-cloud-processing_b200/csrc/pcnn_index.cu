@@ -488,7 +488,7 @@ int pcnn_set_option(pcnn_index* index, const char* name, int value) {
         PCNN_CHECK_ARG(value >= 2 && value <= 6, "pcnn_set_option: radius_leaf_level must be 2..6");
         index->opt_radius_leaf_level = value;
     } else if (!std::strcmp(name, "sort_bits")) {
-        PCNN_CHECK_ARG(value >= 3 && value <= 30 && value % 3 == 0, "pcnn_set_option: sort_bits must be a multiple of 3 in 3..30");
+        PCNN_CHECK_ARG(value >= 3 && value <= 63, "pcnn_set_option: sort_bits must be in 3..63");
         index->opt_sort_bits = value;
     } else if (!std::strcmp(name, "coherent_budget2")) {
         PCNN_CHECK_ARG(value >= 0, "pcnn_set_option: coherent_budget2 must be >= 0");

@@ -33,8 +33,11 @@ __global__ void query_code_kernel(const float* __restrict__ q, int nq, int strid
     perm[i] = (unsigned)i;
 }
 
+int sort_queries_fine(const pcnn_index* ix, const float* q, int64_t nq, int stride, int bits, unsigned** perm_out,
+                      Scratch& sc, cudaStream_t s);
 int sort_queries(const pcnn_index* ix, const float* q, int64_t nq, int stride, unsigned** perm_out,
                  Scratch& sc, cudaStream_t s) {
+    if (ix->opt_sort_bits > 32) return sort_queries_fine(ix, q, nq, stride, ix->opt_sort_bits, perm_out, sc, s);  // 64-bit keys
     NvtxRange nvtx_(ix, "pcnn.query_order");
     const int n = (int)nq;
     unsigned *c0, *c1, *p0, *p1, *hist;

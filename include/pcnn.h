@@ -135,7 +135,8 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
  * Methods 1, 4, 5, 6, 8, 10 and radius kernels 2, 3 are measured-slower variants that exist only in
  * the study build (`make -C .../csrc STUDY=1` -> libpcnn_study.so, -DPCNN_STUDY); this library
  * answers PCNN_ERR_UNSUPPORTED for them.
- * `sort_bits` (3..30, multiple of 3): leading Morton bits the query batch is ordered by.
+ * `sort_bits` (3..63, default 32): leading Morton bits the query batch is ordered by; up to 32 the
+ * keys are 32-bit (four radix passes), beyond that 64-bit (more passes than the finer order repays).
  * `radius_batch`: radius kernel, 1 = auto (default), 0 = warp per query, depth first (also the
  * fallback for clouds of 2^30 points and more), 4 = warp per query with a dense stack walk (auto
  * for sparse batches), 5 = dense stack walk per run of queries (auto for batches as dense as the

@@ -11,6 +11,8 @@ pts, nrm, qry = bench.make_clouds(0)
 dev = torch.device("cuda", 0)
 ix = pc.Index(torch.from_numpy(pts).to(dev))
 ix.set_option("profile", 1)
+if os.environ.get("SORT_BITS"):
+    ix.set_option("sort_bits", int(os.environ["SORT_BITS"]))
 if os.environ.get("METHOD"):  # a study variant (PCNN_LIB=.../libpcnn_study.so)
     ix.set_option("method", int(os.environ["METHOD"]))
 dq = torch.from_numpy(qry).to(dev)

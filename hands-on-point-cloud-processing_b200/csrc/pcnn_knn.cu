@@ -334,7 +334,10 @@ knn_coherent_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
 // scanning ITS OWN next group in lock step -- in a coherent warp those are the same addresses
 // (broadcast loads), in a warp that straddles a jump of the curve the lanes work on different
 // places at the same time.  The warp then pays for the largest per-lane need, not for the sum.
-constexpr int KQ_DEPTH = 8;  // queue entries per lane
+#ifndef PCNN_KQ_DEPTH
+#define PCNN_KQ_DEPTH 8
+#endif
+constexpr int KQ_DEPTH = PCNN_KQ_DEPTH;  // queue entries per lane
 
 template <int K>
 __device__ __forceinline__ void scan_own_group(const IndexView& iv, int g, bool active, float qxf, float qyf,
@@ -693,7 +696,10 @@ knn_queue_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
 // time.  A lane whose walk drags on (poor Morton seed) switches to a boxes-only pass over the
 // rest of its window that tightens its bound from the far corners of full leaf boxes, then
 // resumes.
-constexpr int KL_WALK = 8;  // box steps per round
+#ifndef PCNN_KL_WALK
+#define PCNN_KL_WALK 12
+#endif
+constexpr int KL_WALK = PCNN_KL_WALK;  // box steps per round
 
 #ifdef PCNN_STUDY  // measured-slower variant kept for study: not in the shipped library
 template <int K>

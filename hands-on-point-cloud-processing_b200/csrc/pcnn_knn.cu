@@ -1359,6 +1359,10 @@ constexpr int KH_CAP = 32;
 #ifndef PCNN_KH_QDEPTH
 #define PCNN_KH_QDEPTH 4
 #endif
+#ifndef PCNN_KH_WALK
+#define PCNN_KH_WALK 20  /* 12 / 16 / 20 steps: 292 / 297 / 299 M queries/s at k = 32 on 1M x 1M */
+#endif
+constexpr int KH_WALK = PCNN_KH_WALK;  // box steps per round of the heap kernel
 constexpr int KH_QDEPTH = PCNN_KH_QDEPTH;  // queue entries per lane in the heap kernel (shared memory decides its occupancy)
 
 // Entries are (float32 key rounded up, position in the Morton-ordered array) as in TopKf: 8 bytes instead
@@ -1496,7 +1500,7 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
         n = h >> l;
         while (true) {
 #pragma unroll 1
-            for (int s = 0; s < KL_WALK; s++) {
+            for (int s = 0; s < KH_WALK; s++) {
                 const bool can = !done && cnt <= KH_QDEPTH - 2 && !(cnt > 0 && wf > 3.0e38f);
                 if (!__any_sync(full, can)) break;
                 if (can) {

@@ -17,8 +17,14 @@
 
 namespace pcnn {
 
-constexpr int LS_QDEPTH = 4;  // queued groups per lane
-constexpr int LS_WALK = 8;    // steps per round
+#ifndef PCNN_LS_QDEPTH
+#define PCNN_LS_QDEPTH 4
+#endif
+#ifndef PCNN_LS_WALK
+#define PCNN_LS_WALK 16  /* 6 / 8 / 12 / 16 steps: 1M p2plane 178 / 175 / 174 / 173 us per iteration */
+#endif
+constexpr int LS_QDEPTH = PCNN_LS_QDEPTH;  // queued groups per lane
+constexpr int LS_WALK = PCNN_LS_WALK;    // steps per round
 
 template <class BEST>
 __device__ __forceinline__ void nn1_scan_group(const IndexView& iv, int g, float qx, float qy, float qz,

@@ -991,6 +991,10 @@ constexpr int KW_PLEVELS = 24;
 #define PCNN_KD_THREADS 128
 #endif
 constexpr int KD_THREADS = PCNN_KD_THREADS;  // threads per block of knn_dfs_kernel
+#ifndef PCNN_KD_STRATA
+#define PCNN_KD_STRATA 24  /* measured 0 (curve order) / 4 / 8 / 12 / 16 / 24 / 32 / 37 / 64 / 148 / 1184: k=8 0.855 / 0.838 / 0.822 / 0.802 / 0.787 / 0.785 / 0.779 / 0.793 / 0.884 / 0.920 / 0.804 ms, k=16 1.565 / 1.549 / 1.527 / 1.500 / 1.498 / 1.483 / 1.641 / 1.491 / 1.647 / 1.719 / 1.539 */
+#endif
+constexpr int KD_STRATA = PCNN_KD_STRATA;   // launch-order interleave (0 = curve order)
 
 template <int K>
 __global__ void __launch_bounds__(KD_THREADS, (K <= 8 ? PCNN_DFS_MINBLOCKS : PCNN_DFS_MINBLOCKS16) * (128 / KD_THREADS))
@@ -1004,7 +1008,16 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     pdl_prologue();
     const unsigned full = 0xffffffffu;
     const int tid = threadIdx.x;
-    const int t = blockIdx.x * KD_THREADS + tid;
+    // Launch order: block b of the grid takes slice (b % S) * per + b / S of the ordered batch, so blocks
+    // launched one after another come from S different places on the curve.  Hard regions are contiguous
+    // runs of the curve (tools/warp_times.py); in curve order a hard run at the end is the kernel's tail.
+    int bid = blockIdx.x;
+    if constexpr (KD_STRATA > 1) {
+        const int per = (int)gridDim.x / KD_STRATA;
+        bid = ((int)blockIdx.x % KD_STRATA) * per + (int)blockIdx.x / KD_STRATA;
+        if ((long long)bid * KD_THREADS >= nq) return;
+    }
+    const int t = bid * KD_THREADS + tid;
     unsigned long long dbg_t0 = 0, dbg_c0 = 0;
     if (dbg) {
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
@@ -1362,6 +1375,10 @@ constexpr int KH_CAP = 32;
 #ifndef PCNN_KH_WALK
 #define PCNN_KH_WALK 20  /* 12 / 16 / 20 steps: 292 / 297 / 299 M queries/s at k = 32 on 1M x 1M */
 #endif
+#ifndef PCNN_KH_STRATA
+#define PCNN_KH_STRATA 24
+#endif
+constexpr int KH_STRATA = PCNN_KH_STRATA;
 constexpr int KH_WALK = PCNN_KH_WALK;  // box steps per round of the heap kernel
 constexpr int KH_QDEPTH = PCNN_KH_QDEPTH;  // queue entries per lane in the heap kernel (shared memory decides its occupancy)
 
@@ -1456,7 +1473,13 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
     __shared__ float s_ql[KH_QDEPTH][KH_THREADS];
     const unsigned full = 0xffffffffu;
     const int tid = threadIdx.x;
-    const int t = blockIdx.x * KH_THREADS + tid;
+    int bid = blockIdx.x;  // launch order interleaved over the curve, as knn_dfs_kernel
+    if constexpr (KH_STRATA > 1) {
+        const int per = (int)gridDim.x / KH_STRATA;
+        bid = ((int)blockIdx.x % KH_STRATA) * per + (int)blockIdx.x / KH_STRATA;
+        if ((long long)bid * KH_THREADS >= nq) return;
+    }
+    const int t = bid * KH_THREADS + tid;
     const bool live = t < nq;
     const int tt = live ? t : nq - 1;
     const int qi = perm ? (int)perm[tt] : tt;
@@ -1850,7 +1873,9 @@ static void launch_lockstep_k(const pcnn_index* ix, const float* q, int nq, int 
 template <int K>
 static void launch_dfs_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
                          int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
-    launch_pdl(knn_dfs_kernel<K>, dim3((nq + KD_THREADS - 1) / KD_THREADS), dim3(KD_THREADS), s, ix->opt_pdl != 0 && perm != nullptr,
+    int nb = (nq + KD_THREADS - 1) / KD_THREADS;
+    if constexpr (KD_STRATA > 1) nb = ((nb + KD_STRATA - 1) / KD_STRATA) * KD_STRATA;
+    launch_pdl(knn_dfs_kernel<K>, dim3(nb), dim3(KD_THREADS), s, ix->opt_pdl != 0 && perm != nullptr,
                ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
 }
 #ifdef PCNN_STUDY
@@ -1911,7 +1936,9 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
             if (rc != PCNN_OK) return rc;
         }
         prof_begin(ix, s);
-        knn_dfs_heap_kernel<<<(nq + KH_THREADS - 1) / KH_THREADS, KH_THREADS, 0, s>>>(
+        int nbh = (nq + KH_THREADS - 1) / KH_THREADS;
+        if constexpr (KH_STRATA > 1) nbh = ((nbh + KH_STRATA - 1) / KH_STRATA) * KH_STRATA;
+        knn_dfs_heap_kernel<<<nbh, KH_THREADS, 0, s>>>(
             ix->view, q, nq, stride, perm, k, out_idx, out_dist, out_dist64);
         prof_end(ix, s);
 #ifdef PCNN_STUDY

@@ -994,6 +994,9 @@ constexpr int KD_THREADS = PCNN_KD_THREADS;  // threads per block of knn_dfs_ker
 #ifndef PCNN_KD_STRATA
 #define PCNN_KD_STRATA 24  /* measured 0 (curve order) / 4 / 8 / 12 / 16 / 24 / 32 / 37 / 64 / 148 / 1184: k=8 0.855 / 0.838 / 0.822 / 0.802 / 0.787 / 0.785 / 0.779 / 0.793 / 0.884 / 0.920 / 0.804 ms, k=16 1.565 / 1.549 / 1.527 / 1.500 / 1.498 / 1.483 / 1.641 / 1.491 / 1.647 / 1.719 / 1.539 */
 #endif
+#ifndef PCNN_KD_STRATA_ORDERED_ONLY
+#define PCNN_KD_STRATA_ORDERED_ONLY 1  // batches searched in the caller's order keep the caller's launch order
+#endif
 constexpr int KD_STRATA = PCNN_KD_STRATA;   // launch-order interleave (0 = curve order)
 
 template <int K>
@@ -1012,7 +1015,7 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
     // launched one after another come from S different places on the curve.  Hard regions are contiguous
     // runs of the curve (tools/warp_times.py); in curve order a hard run at the end is the kernel's tail.
     int bid = blockIdx.x;
-    if constexpr (KD_STRATA > 1) {
+    if (KD_STRATA > 1 && (perm != nullptr || !PCNN_KD_STRATA_ORDERED_ONLY)) {
         const int per = (int)gridDim.x / KD_STRATA;
         bid = ((int)blockIdx.x % KD_STRATA) * per + (int)blockIdx.x / KD_STRATA;
         if ((long long)bid * KD_THREADS >= nq) return;
@@ -1874,7 +1877,7 @@ template <int K>
 static void launch_dfs_k(const pcnn_index* ix, const float* q, int nq, int stride, const unsigned* perm,
                          int k, int32_t* oi, float* od, double* od64, cudaStream_t s) {
     int nb = (nq + KD_THREADS - 1) / KD_THREADS;
-    if constexpr (KD_STRATA > 1) nb = ((nb + KD_STRATA - 1) / KD_STRATA) * KD_STRATA;
+    if (KD_STRATA > 1 && (perm != nullptr || !PCNN_KD_STRATA_ORDERED_ONLY)) nb = ((nb + KD_STRATA - 1) / KD_STRATA) * KD_STRATA;
     launch_pdl(knn_dfs_kernel<K>, dim3(nb), dim3(KD_THREADS), s, ix->opt_pdl != 0 && perm != nullptr,
                ix->view, q, nq, stride, perm, k, oi, od, od64, ix->dbg_warp_times);
 }

@@ -804,12 +804,23 @@ __global__ void icp_state_init_kernel(Dev* st, const float* __restrict__ T0) {
     }
 }
 
+#ifndef PCNN_NN1_STRATA
+#define PCNN_NN1_STRATA 24
+#endif
+constexpr int NN1_STRATA = PCNN_NN1_STRATA;
+
 __global__ void __launch_bounds__(128)
 nn1_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride, const unsigned* __restrict__ perm,
            int32_t* __restrict__ out_idx, float* __restrict__ out_d2) {
     __shared__ int s_qg[LS_QDEPTH][128];
     __shared__ float s_ql[LS_QDEPTH][128];
-    const int t = blockIdx.x * 128 + threadIdx.x;
+    int bid = blockIdx.x;  // launch order interleaved over the ordered batch (pcnn_knn.cu, KD_STRATA)
+    if (NN1_STRATA > 1 && perm != nullptr) {
+        const int per = (int)gridDim.x / NN1_STRATA;
+        bid = ((int)blockIdx.x % NN1_STRATA) * per + (int)blockIdx.x / NN1_STRATA;
+        if ((long long)bid * 128 >= nq) return;
+    }
+    const int t = bid * 128 + threadIdx.x;
     const bool live = t < nq;
     const int tt = live ? t : nq - 1;  // tail lanes shadow the last query: warps stay whole
     const int qi = perm ? (int)perm[tt] : tt;
@@ -859,7 +870,9 @@ int launch_nn1(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         int rc = sort_queries(ix, q, nq, stride, &perm, sc, s);
         if (rc != PCNN_OK) return rc;
     }
-    nn1_kernel<<<(nq + 127) / 128, 128, 0, s>>>(ix->view, q, nq, stride, perm, out_idx, out_d2);
+    int nb = (nq + 127) / 128;
+    if (NN1_STRATA > 1 && perm != nullptr) nb = ((nb + NN1_STRATA - 1) / NN1_STRATA) * NN1_STRATA;
+    nn1_kernel<<<nb, 128, 0, s>>>(ix->view, q, nq, stride, perm, out_idx, out_d2);
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;
 }

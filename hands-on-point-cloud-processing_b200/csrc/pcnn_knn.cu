@@ -66,6 +66,7 @@ int sort_queries(const pcnn_index* ix, const float* q, int64_t nq, int stride, u
 __global__ void query_code64_kernel(const float* __restrict__ q, int nq, int stride,
                                     const float* __restrict__ cube, int bits,
                                     unsigned long long* __restrict__ codes, unsigned* __restrict__ perm) {
+    pdl_prologue();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nq) return;
     const float* p = q + (size_t)i * stride;
@@ -84,8 +85,9 @@ int sort_queries_fine(const pcnn_index* ix, const float* q, int64_t nq, int stri
     PCNN_CUDA(sc.get(&p0, (size_t)n));
     PCNN_CUDA(sc.get(&p1, (size_t)n));
     PCNN_CUDA(sc.get(&hist, radix_hist_elems(n)));
-    query_code64_kernel<<<(n + 255) / 256, 256, 0, s>>>(q, n, stride, ix->cube, bits, c0, p0);
-    int where = radix_sort_pairs<unsigned long long>(c0, p0, c1, p1, hist, n, bits, s);
+    const bool pdl = ix->opt_pdl != 0;
+    launch_pdl(query_code64_kernel, dim3((n + 255) / 256), dim3(256), s, pdl, q, n, stride, (const float*)ix->cube, bits, c0, p0);
+    int where = radix_sort_pairs<unsigned long long>(c0, p0, c1, p1, hist, n, bits, s, pdl);
     *perm_out = where ? p1 : p0;
     PCNN_CUDA(cudaGetLastError());
     return PCNN_OK;

@@ -168,8 +168,14 @@ __global__ void gather_kernel(const float* __restrict__ xyz, int n, int stride,
 
 __global__ void box_level0(const float4* __restrict__ pts, int n, int n0, float4* __restrict__ box) {
     int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= n0) return;
     const float inf = __int_as_float(0x7f800000);
+    if (g >= n0) {
+        if (g == n0 && (n0 & 1) && n0 > 1) {  // the empty box behind an odd level
+            box[2 * (size_t)g] = make_float4(inf, inf, inf, 0.f);
+            box[2 * (size_t)g + 1] = make_float4(-inf, -inf, -inf, 0.f);
+        }
+        return;
+    }
     float4 lo = make_float4(inf, inf, inf, 0.f), hi = make_float4(-inf, -inf, -inf, 0.f);
     int first = g << PCNN_GROUP_LOG;
 #pragma unroll
@@ -187,7 +193,14 @@ __global__ void box_level0(const float4* __restrict__ pts, int n, int n0, float4
 __global__ void box_up(const float4* __restrict__ child, int nchild, float4* __restrict__ parent,
                        int nparent) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nparent) return;
+    if (i >= nparent) {
+        if (i == nparent && (nparent & 1) && nparent > 1) {  // the empty box behind an odd level
+            const float inf = __int_as_float(0x7f800000);
+            parent[2 * (size_t)i] = make_float4(inf, inf, inf, 0.f);
+            parent[2 * (size_t)i + 1] = make_float4(-inf, -inf, -inf, 0.f);
+        }
+        return;
+    }
     float4 lo = child[2 * (size_t)(2 * i)], hi = child[2 * (size_t)(2 * i) + 1];
     if (2 * i + 1 < nchild) {
         float4 lo2 = child[2 * (size_t)(2 * i + 1)], hi2 = child[2 * (size_t)(2 * i + 1) + 1];
@@ -236,7 +249,9 @@ static int build_impl(pcnn_index** out, int kind, const float* xyz_dev, int64_t 
     size_t nboxes = 0;
     for (int c = n0; c >= 1; c = (c + 1) / 2) {
         v.lev_off[v.nlev++] = (int)nboxes;
-        nboxes += (size_t)c;
+        // a level with an odd number of nodes is followed by one EMPTY box (lo = +inf, hi = -inf: every lower
+        // bound against it is +inf), so that the walks load the two boxes of a pair unconditionally
+        nboxes += (size_t)c + (size_t)(c > 1 ? (c & 1) : 0);
         if (c == 1) break;
     }
     if (n0 == 0) { v.nlev = 1; v.lev_off[0] = 0; nboxes = 1; }
@@ -282,11 +297,11 @@ static int build_impl(pcnn_index** out, int kind, const float* xyz_dev, int64_t 
         morton_kernel<<<G, T, 0, s>>>(xyz_dev, ni, stride, ix->cube, c0, p0);
         int where = radix_sort_pairs<unsigned long long>(c0, p0, c1, p1, hist, ni, 3 * PCNN_MORTON_BITS, s);
         gather_kernel<<<G, T, 0, s>>>(xyz_dev, ni, stride, where ? p1 : p0, where ? c1 : c0, ix->pts, ix->gcode);
-        box_level0<<<(n0 + T - 1) / T, T, 0, s>>>(ix->pts, ni, n0, ix->box);
+        box_level0<<<(n0 + 1 + T - 1) / T, T, 0, s>>>(ix->pts, ni, n0, ix->box);
         int cnt = n0;
         for (int l = 1; l < v.nlev; l++) {
             int pc = (cnt + 1) / 2;
-            box_up<<<(pc + T - 1) / T, T, 0, s>>>(ix->box + 2 * (size_t)v.lev_off[l - 1], cnt,
+            box_up<<<(pc + 1 + T - 1) / T, T, 0, s>>>(ix->box + 2 * (size_t)v.lev_off[l - 1], cnt,
                                                    ix->box + 2 * (size_t)v.lev_off[l], pc);
             cnt = pc;
         }

@@ -1093,20 +1093,16 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
                         // examine the two children of (l, n)
                         c_steps++;
                         const int L = l - 1, P = 2 * n;
-                        const int cl = (int)(((unsigned)iv.n0 + (1u << L) - 1u) >> L);
+                        // both boxes of the pair, unconditionally: a node without a sibling is followed by an
+                        // empty box (pcnn_index.cu), whose lower bound is +inf
                         const float4* b = iv.box + 2 * ((size_t)iv.lev_off[L] + P);
-                        const float4 alo = __ldg(b), ahi = __ldg(b + 1);
+                        const float4 alo = __ldg(b), ahi = __ldg(b + 1), blo = __ldg(b + 2), bhi = __ldg(b + 3);
                         const float lbA = lbsq32x(boxgap_rd(alo.x, ahi.x, qxf), boxgap_rd(alo.y, ahi.y, qyf),
                                                   boxgap_rd(alo.z, ahi.z, qzf));
-                        float lbB = INFf;
-                        const bool hasB = P + 1 < cl;
-                        if (hasB) {
-                            const float4 blo = __ldg(b + 2), bhi = __ldg(b + 3);
-                            lbB = lbsq32x(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
-                                          boxgap_rd(blo.z, bhi.z, qzf));
-                        }
+                        const float lbB = lbsq32x(boxgap_rd(blo.x, bhi.x, qxf), boxgap_rd(blo.y, bhi.y, qyf),
+                                                  boxgap_rd(blo.z, bhi.z, qzf));
                         bool first1 = lbB < lbA;
-                        if (hasB && lbB == lbA)  // tie (query inside both boxes): follow the curve
+                        if (lbB == lbA)  // tie (query inside both boxes): follow the curve
                             first1 = qcode >= __ldg(iv.gcode + ((size_t)(P + 1) << L));
                         const float lbn = first1 ? lbB : lbA, lbf2 = first1 ? lbA : lbB;
                         const int near = P + (first1 ? 1 : 0);

@@ -1380,6 +1380,9 @@ constexpr int KH_CAP = 32;
 #ifndef PCNN_KH_STRATA
 #define PCNN_KH_STRATA 24
 #endif
+#ifndef PCNN_KH_SCAN2
+#define PCNN_KH_SCAN2 1
+#endif
 constexpr int KH_STRATA = PCNN_KH_STRATA;
 constexpr int KH_WALK = PCNN_KH_WALK;  // box steps per round of the heap kernel
 constexpr int KH_QDEPTH = PCNN_KH_QDEPTH;  // queue entries per lane in the heap kernel (shared memory decides its occupancy)
@@ -1459,6 +1462,42 @@ __device__ __forceinline__ void scan_own_group_heap(const IndexView& iv, int g, 
             const float f = ru32(key64(p.x, p.y, p.z, qx, qy, qz));
             if (hp.accepts(f, first + j)) {
                 hp.replace_root(f, first + j);
+                wf = fminf(wf, hp.K(0));
+            }
+        }
+    }
+}
+
+// two queued groups per call (as scan_own_groups2_f): the replacement rounds are shared by 16 points' survivors
+__device__ __forceinline__ void scan_own_groups2_heap(const IndexView& iv, int g0, bool act0, int g1, bool act1,
+                                                      float qxf, float qyf, float qzf, double qx, double qy, double qz,
+                                                      const HeapRef& hp, float& wf) {
+    const unsigned full = 0xffffffffu;
+    unsigned pass = 0;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        if (h ? act1 : act0) {
+            const int first = (h ? g1 : g0) << PCNN_GROUP_LOG;
+            const int cnt = (iv.n - first) < PCNN_GROUP ? (iv.n - first) : PCNN_GROUP;
+#pragma unroll
+            for (int j = 0; j < PCNN_GROUP; j++) {
+                if (j < cnt) {
+                    const float4 p = __ldg(iv.pts + first + j);
+                    const float lbf = lbsq32x(absdiff_rz(p.x, qxf), absdiff_rz(p.y, qyf), absdiff_rz(p.z, qzf));
+                    if (!(lbf > wf)) pass |= 1u << (h * PCNN_GROUP + j);
+                }
+            }
+        }
+    }
+    while (__any_sync(full, pass != 0)) {
+        if (pass) {
+            const int j = __ffs((int)pass) - 1;
+            pass &= pass - 1;
+            const int pi = ((j < PCNN_GROUP ? g0 : g1) << PCNN_GROUP_LOG) + (j & (PCNN_GROUP - 1));
+            const float4 p = __ldg(iv.pts + pi);
+            const float f = ru32(key64(p.x, p.y, p.z, qx, qy, qz));
+            if (hp.accepts(f, pi)) {
+                hp.replace_root(f, pi);
                 wf = fminf(wf, hp.K(0));
             }
         }
@@ -1587,11 +1626,21 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
             }
             {
                 const int maxc = __reduce_max_sync(full, cnt);
+#if PCNN_KH_SCAN2
+                for (int r = 0; r < maxc; r += 2) {
+                    const bool act0 = r < cnt && !(s_ql[r][tid] > wf);
+                    const bool act1 = r + 1 < cnt && !(s_ql[r + 1][tid] > wf);
+                    if (__any_sync(full, act0 || act1))
+                        scan_own_groups2_heap(iv, act0 ? s_qg[r][tid] : 0, act0, act1 ? s_qg[r + 1][tid] : 0, act1, qxf, qyf, qzf,
+                                              qx, qy, qz, hp, wf);
+                }
+#else
                 for (int r = 0; r < maxc; r++) {
                     const bool act = r < cnt && !(s_ql[r][tid] > wf);
                     if (__any_sync(full, act))
                         scan_own_group_heap(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, hp, wf);
                 }
+#endif
                 cnt = 0;
             }
             if (!__any_sync(full, !done)) break;

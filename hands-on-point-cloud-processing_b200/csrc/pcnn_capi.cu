@@ -115,9 +115,10 @@ int pcnn_knn_host(const pcnn_index* index, const float* q_host, int64_t nq, int 
     // queries, k = 8, against 1.05 ms of search), so what matters is how soon the first result byte
     // leaves and that the copy engine never starves afterwards.  Stages are searched in the CALLER'S
     // order: ordering a stage's queries along the curve is a chain of 13 small dependent kernels that
-    // crawls (0.2-0.6 ms) while another stage's search fills the GPU, and it buys only 0.17-0.23 ms of
-    // search time per million queries (1.05 ms ordered, 1.21 ms on LiDAR scan order, 1.27 ms on a random
-    // shuffle; tools/knn_unsorted.py).  Rows do not depend on the order.  Two small stages lead so that
+    // crawls (0.2-0.6 ms) while another stage's search fills the GPU; what it would buy is search time
+    // (per million queries 0.77 ms ordered, 1.11 ms on LiDAR scan order, 1.18 ms on a random shuffle;
+    // tools/knn_unsorted.py), and the search is not what this call waits for: from 0.25 ms on the D2H
+    // engine is (stage timeline).  Rows do not depend on the order.  Two small stages lead so that
     // results are on the wire after ~0.2 ms.
     struct Stage { int64_t q0, m; int sort; };
     std::vector<Stage> plan;

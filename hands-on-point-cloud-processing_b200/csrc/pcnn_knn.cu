@@ -510,6 +510,53 @@ __device__ __forceinline__ void scan_own_groups2_f(const IndexView& iv, int g0, 
     }
 }
 
+// The first group of a query goes into an EMPTY list: its eight points are keyed and put in order by a
+// 19-comparator network instead of eight insertions.  A lane whose sorted keys tie as floats (or a group
+// that is not full) sends the whole warp through the general path -- rare, and warp-uniform.
+template <int K>
+__device__ __forceinline__ void seed_first_group_f(const IndexView& iv, int g, float qxf, float qyf, float qzf,
+                                                   double qx, double qy, double qz, TopKf<K>& tk, float& wf,
+                                                   int& ins_rounds) {
+    const unsigned full = 0xffffffffu;
+    const int first = g << PCNN_GROUP_LOG;
+    float f[PCNN_GROUP];
+    int ps[PCNN_GROUP];
+    bool odd = iv.n - first < PCNN_GROUP;
+    if (!odd) {
+#pragma unroll
+        for (int j = 0; j < PCNN_GROUP; j++) {
+            const float4 p = __ldg(iv.pts + first + j);
+            f[j] = ru32(key64(p.x, p.y, p.z, qx, qy, qz));
+            ps[j] = first + j;
+        }
+#define KS_CAS(a, b)                                                \
+    {                                                               \
+        const bool sw = f[b] < f[a];                                \
+        const float fa = f[a], fb = f[b];                           \
+        const int pa = ps[a], pb = ps[b];                           \
+        f[a] = sw ? fb : fa; f[b] = sw ? fa : fb;                   \
+        ps[a] = sw ? pb : pa; ps[b] = sw ? pa : pb;                 \
+    }
+        KS_CAS(0, 1) KS_CAS(2, 3) KS_CAS(4, 5) KS_CAS(6, 7)
+        KS_CAS(0, 2) KS_CAS(1, 3) KS_CAS(4, 6) KS_CAS(5, 7)
+        KS_CAS(1, 2) KS_CAS(5, 6) KS_CAS(0, 4) KS_CAS(3, 7)
+        KS_CAS(1, 5) KS_CAS(2, 6)
+        KS_CAS(1, 4) KS_CAS(3, 6)
+        KS_CAS(2, 4) KS_CAS(3, 5)
+        KS_CAS(3, 4)
+#undef KS_CAS
+#pragma unroll
+        for (int j = 0; j + 1 < PCNN_GROUP; j++) odd |= f[j] == f[j + 1];
+    }
+    if (__any_sync(full, odd)) {
+        scan_own_group_f<K>(iv, g, true, qxf, qyf, qzf, qx, qy, qz, tk, wf, ins_rounds);
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < K && j < PCNN_GROUP; j++) { tk.key[j] = f[j]; tk.pos[j] = ps[j]; }
+    if (K <= PCNN_GROUP) wf = fminf(wf, tk.key[K - 1]);
+}
+
 template <int K>
 __device__ __forceinline__ void write_row_f(const TopKf<K>& tk, const float4* __restrict__ pts, double qx, double qy,
                                             double qz, int64_t row, int k, int32_t* out_idx, float* out_dist,
@@ -877,6 +924,9 @@ knn_lockstep_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
 #ifndef PCNN_KD_SCAN2
 #define PCNN_KD_SCAN2 1
 #endif
+#ifndef PCNN_KD_SEEDNET
+#define PCNN_KD_SEEDNET 1
+#endif
 constexpr int KD_COOP_LANES = PCNN_KD_COOP_LANES, KD_COOP_ROUNDS = PCNN_KD_COOP_ROUNDS;
 
 template <int K, int THREADS, int QDEPTH, int PLEVELS>
@@ -1053,7 +1103,11 @@ knn_dfs_kernel(IndexView iv, const float* __restrict__ q, int nq, int stride,
         const int h = home_group(iv, qcode);
         const int h0 = h > 0 ? h - 1 : 0, h1 = (h + 1 < iv.n0) ? h + 1 : iv.n0 - 1;
         // (the home group first: its bound spares its neighbours most of their insertions)
+#if PCNN_KD_SEEDNET
+        seed_first_group_f<K>(iv, h, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
+#else
         scan_own_group_f<K>(iv, h, true, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
+#endif
         if constexpr (PCNN_KD_SCAN2 && K <= 8) {
             scan_own_groups2_f<K>(iv, h0, h0 < h, h1, h1 > h, qxf, qyf, qzf, qx, qy, qz, tk, wf, c_ins);
         } else {

@@ -1437,10 +1437,16 @@ constexpr int KH_CAP = 32;
 #ifndef PCNN_KH_SCAN2
 #define PCNN_KH_SCAN2 1
 #endif
+#ifndef PCNN_KH_FILL
+#define PCNN_KH_FILL 1
+#endif
 constexpr int KH_STRATA = PCNN_KH_STRATA;
 constexpr int KH_WALK = PCNN_KH_WALK;  // box steps per round of the heap kernel
 constexpr int KH_QDEPTH = PCNN_KH_QDEPTH;  // queue entries per lane in the heap kernel (shared memory decides its occupancy)
 
+#ifndef PCNN_KH_FILL
+#define PCNN_KH_FILL 1
+#endif
 // Entries are (float32 key rounded up, position in the Morton-ordered array) as in TopKf: 8 bytes instead
 // of 12, one FSETP per comparison, exact double keys + original indices only where two floats are equal.
 struct HeapRef {
@@ -1479,6 +1485,28 @@ struct HeapRef {
         I(i) = p;
     }
     __device__ __forceinline__ void replace_root(float f, int p) const { sift(0, k, f, p); }
+    // bottom-up construction over all k slots (slots never filled hold +inf / -1 and sink nowhere)
+    __device__ __forceinline__ void heapify() const {
+        for (int i = k / 2 - 1; i >= 0; i--) sift(i, k, K(i), I(i));
+    }
+    // One candidate.  The first k go into the slots as they come and the heap is built once when the
+    // k-th has arrived (O(k) instead of k sift-downs through a heap of +inf); from then on a candidate
+    // that beats the root replaces it.  Returns true when the root (the pruning bound) may have changed.
+    __device__ __forceinline__ bool offer(float f, int p, int& filled) const {
+#if PCNN_KH_FILL
+        if (filled < k) {
+            K(filled) = f;
+            I(filled) = p;
+            filled++;
+            if (filled < k) return false;
+            heapify();
+            return true;
+        }
+#endif
+        if (!accepts(f, p)) return false;
+        replace_root(f, p);
+        return true;
+    }
     // heap -> ascending order in place
     __device__ __forceinline__ void sort() const {
         for (int n = k - 1; n > 0; n--) {
@@ -1493,7 +1521,7 @@ struct HeapRef {
 
 __device__ __forceinline__ void scan_own_group_heap(const IndexView& iv, int g, bool active, float qxf, float qyf,
                                                     float qzf, double qx, double qy, double qz,
-                                                    const HeapRef& hp, float& wf) {
+                                                    const HeapRef& hp, float& wf, int& filled) {
     const unsigned full = 0xffffffffu;
     const int first = g << PCNN_GROUP_LOG;
     unsigned pass = 0;
@@ -1514,10 +1542,7 @@ __device__ __forceinline__ void scan_own_group_heap(const IndexView& iv, int g, 
             pass &= pass - 1;
             const float4 p = __ldg(iv.pts + first + j);
             const float f = ru32(key64(p.x, p.y, p.z, qx, qy, qz));
-            if (hp.accepts(f, first + j)) {
-                hp.replace_root(f, first + j);
-                wf = fminf(wf, hp.K(0));
-            }
+            if (hp.offer(f, first + j, filled)) wf = fminf(wf, hp.K(0));
         }
     }
 }
@@ -1525,7 +1550,7 @@ __device__ __forceinline__ void scan_own_group_heap(const IndexView& iv, int g, 
 // two queued groups per call (as scan_own_groups2_f): the replacement rounds are shared by 16 points' survivors
 __device__ __forceinline__ void scan_own_groups2_heap(const IndexView& iv, int g0, bool act0, int g1, bool act1,
                                                       float qxf, float qyf, float qzf, double qx, double qy, double qz,
-                                                      const HeapRef& hp, float& wf) {
+                                                      const HeapRef& hp, float& wf, int& filled) {
     const unsigned full = 0xffffffffu;
     unsigned pass = 0;
 #pragma unroll
@@ -1550,10 +1575,7 @@ __device__ __forceinline__ void scan_own_groups2_heap(const IndexView& iv, int g
             const int pi = ((j < PCNN_GROUP ? g0 : g1) << PCNN_GROUP_LOG) + (j & (PCNN_GROUP - 1));
             const float4 p = __ldg(iv.pts + pi);
             const float f = ru32(key64(p.x, p.y, p.z, qx, qy, qz));
-            if (hp.accepts(f, pi)) {
-                hp.replace_root(f, pi);
-                wf = fminf(wf, hp.K(0));
-            }
+            if (hp.offer(f, pi, filled)) wf = fminf(wf, hp.K(0));
         }
     }
 }
@@ -1588,6 +1610,7 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
     hp.pts = iv.pts;
     hp.qx = qx; hp.qy = qy; hp.qz = qz;
     hp.init();
+    int filled = 0;  // slots taken before the heap was built (HeapRef::offer)
     if (iv.n > 0) {
         const float INFf = __int_as_float(0x7f800000);
         float wf = INFf;
@@ -1609,7 +1632,7 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
             const int maxc = __reduce_max_sync(full, cnt);
             for (int r = 0; r < maxc; r++) {
                 const bool act = r < cnt;
-                scan_own_group_heap(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, hp, wf);
+                scan_own_group_heap(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, hp, wf, filled);
             }
             cnt = 0;
         }
@@ -1686,13 +1709,13 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
                     const bool act1 = r + 1 < cnt && !(s_ql[r + 1][tid] > wf);
                     if (__any_sync(full, act0 || act1))
                         scan_own_groups2_heap(iv, act0 ? s_qg[r][tid] : 0, act0, act1 ? s_qg[r + 1][tid] : 0, act1, qxf, qyf, qzf,
-                                              qx, qy, qz, hp, wf);
+                                              qx, qy, qz, hp, wf, filled);
                 }
 #else
                 for (int r = 0; r < maxc; r++) {
                     const bool act = r < cnt && !(s_ql[r][tid] > wf);
                     if (__any_sync(full, act))
-                        scan_own_group_heap(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, hp, wf);
+                        scan_own_group_heap(iv, act ? s_qg[r][tid] : 0, act, qxf, qyf, qzf, qx, qy, qz, hp, wf, filled);
                 }
 #endif
                 cnt = 0;
@@ -1700,6 +1723,7 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
             if (!__any_sync(full, !done)) break;
         }
     }
+    if (PCNN_KH_FILL && filled < k) hp.heapify();  // fewer than k candidates in all: the slots are not a heap yet
     hp.sort();
     if (live) {
         for (int j = 0; j < k; j++) {

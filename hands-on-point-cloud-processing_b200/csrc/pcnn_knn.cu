@@ -4,16 +4,22 @@
 // (Homework2/hw2/include/benchmark.hpp:59-66): `KNNResultSet rs(k); KDTreeKNNSearch(...)`
 // (kdtree.hpp:329-364) / `OctreeKNNSearch(...)` (octree.hpp:143-186).
 //
-// Three kernels, one result contract (k smallest under (d2 double, original index)):
-//   knn_thread_kernel<K>  one query per thread, sorted top-K in registers, stackless sweep
-//                         of the implicit AABB hierarchy; queries are first ordered along
-//                         the Morton curve so a warp walks neighbouring nodes (k <= 16)
-//   knn_warp_kernel       one query per warp, 32 candidates / 32 child boxes per step,
-//                         nearest-first descent, top-k list distributed over the lanes and
-//                         updated with ballots + shuffles (k <= 32; larger k in passes)
-//   knn_brute_kernel<K>   brute-force tiles: the cloud streamed through shared memory with
-//                         bulk async copies (TMA, cp.async.bulk + mbarrier), one query per
-//                         thread; small clouds and the FP64-pipe-bound reference point
+// One result contract -- the k smallest under (squared distance in double, original index), rows in that
+// order (resultSet.hpp:65-91) -- and four kernels in the shipped library:
+//   knn_dfs_kernel<K>     k <= 16 (method 7, the headline kernel): one query per lane, 32 queries of the
+//                         Morton-ordered batch per warp, lock-step nearest-first walks of the implicit AABB
+//                         hierarchy in rounds of 12 box steps, queued groups drained together; the k best
+//                         as (float32 key rounded up, position) ordered exactly (TopKf); deferred siblings
+//                         remembered with their bounds; launch order interleaved over the curve; a warp's
+//                         last walks finished cooperatively
+//   knn_dfs_heap_kernel   16 < k <= 32 (method 9): the same walk, the k best in a per-lane max-heap in shared
+//                         memory
+//   knn_warp_kernel       k > 32 (method 2): one query per warp, 32 child boxes / 32 candidates per step, the
+//                         list distributed over the lanes; larger k in passes of 32
+//   knn_brute_kernel<K>   method 3: the cloud streamed through shared memory by 1-D bulk async copies
+//                         (cp.async.bulk + mbarrier), one query per thread; tiny clouds and the FP64-bound
+//                         reference point
+// The measured-slower variants (methods 1, 4, 5, 6, 8, 10) exist in the -DPCNN_STUDY build only.
 #include "pcnn_internal.cuh"
 #include "pcnn_search.cuh"
 #include "pcnn_sort.cuh"

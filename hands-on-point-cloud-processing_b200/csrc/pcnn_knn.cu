@@ -1597,7 +1597,7 @@ knn_dfs_heap_kernel(IndexView iv, const float* __restrict__ q, int nq, int strid
     const unsigned full = 0xffffffffu;
     const int tid = threadIdx.x;
     int bid = blockIdx.x;  // launch order interleaved over the curve, as knn_dfs_kernel
-    if constexpr (KH_STRATA > 1) {
+    if (KH_STRATA > 1 && perm != nullptr) {  // only batches the library ordered itself (as knn_dfs_kernel)
         const int per = (int)gridDim.x / KH_STRATA;
         bid = ((int)blockIdx.x % KH_STRATA) * per + (int)blockIdx.x / KH_STRATA;
         if ((long long)bid * KH_THREADS >= nq) return;
@@ -2072,7 +2072,7 @@ int launch_knn(const pcnn_index* ix, const float* q, int64_t nq64, int stride, i
         }
         prof_begin(ix, s);
         int nbh = (nq + KH_THREADS - 1) / KH_THREADS;
-        if constexpr (KH_STRATA > 1) nbh = ((nbh + KH_STRATA - 1) / KH_STRATA) * KH_STRATA;
+        if (KH_STRATA > 1 && perm != nullptr) nbh = ((nbh + KH_STRATA - 1) / KH_STRATA) * KH_STRATA;
         knn_dfs_heap_kernel<<<nbh, KH_THREADS, 0, s>>>(
             ix->view, q, nq, stride, perm, k, out_idx, out_dist, out_dist64);
         prof_end(ix, s);
